@@ -1,0 +1,292 @@
+/* minipath_b200 — C ABI of the B200-native renderer core for minipath's per-pixel trace path.
+ *
+ * The reference (bluecube/minipath, pure Rust) has no FFI of its own; the boundary this library sits
+ * behind is the crate's public Rust API (`render`, `RenderSettings`, `RenderProgress`, `Camera`,
+ * `Scene<TriangleBvh>`; reference src/lib.rs:8-10).  Every entry point below names the reference
+ * item (file:line under the reference tree) it replaces.  INTEGRATION.md shows the Rust `-sys` binding.
+ *
+ * Conventions: plain C types only; every function returns 0 on success and a negative MP_E* code on
+ * failure (message via mp_last_error(), thread-local); nothing throws across the ABI; one MpCtx per GPU,
+ * calls on one context are serialised by the caller (mirrors one Worker per thread,
+ * reference src/renderer/worker.rs:15-20).  There is NO CPU fallback: without a CUDA device every
+ * device entry point fails with MP_ENODEVICE.
+ */
+#ifndef MINIPATH_B200_H
+#define MINIPATH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MP_OK 0
+#define MP_EINVAL (-1)
+#define MP_ECUDA (-2)
+#define MP_ENODEVICE (-3)
+#define MP_EIO (-4)
+#define MP_ESTATE (-5)
+#define MP_ENOMEM (-6)
+
+/* ---- node links: reference src/scene/triangle_bvh/mod.rs:57-114 (CompressedNodeLink) ---- */
+#define MP_LINK_COUNT_BITS 3u
+#define MP_LINK_COUNT_MASK 7u
+#define MP_LINK_NULL 0xFFFFFFF8u        /* (u32::MAX >> 3) << 3, mod.rs:69 */
+#define MP_LINK_MAX_INDEX 0x1FFFFFFEu   /* (u32::MAX >> 3) - 1, mod.rs:71 */
+#define MP_LINK_MAX_COUNT 7u            /* mod.rs:73 */
+#define MP_NO_HIT 0xFFFFFFFFu           /* TriangleIdx::default() == usize::MAX, mod.rs:143-147 */
+#define MP_INNER_NODE_CHILDREN 8        /* mod.rs:14 */
+#define MP_LEAF_PACKET_SIZE 8           /* mod.rs:15 */
+#define MP_LEAF_MAX_TRIANGLES 56        /* mod.rs:16-17 */
+
+/* Encode/decode helpers; return MP_EINVAL where the reference panics (mod.rs:78-87,189-236). */
+int mp_link_new_leaf(uint32_t packet_index, uint32_t packet_count, uint32_t* out_link);
+int mp_link_new_inner(uint32_t node_index, uint32_t* out_link);
+/* kind: 0 = null, 1 = inner, 2 = leaf */
+int mp_link_decode(uint32_t link, int* out_kind, uint32_t* out_index, uint32_t* out_count);
+
+/* ---- flat BVH: device image of reference TriangleBvh (triangle_bvh/mod.rs:20-53) ---- */
+
+/* Enclosing box of a node as carried on the reference's traversal stack (WorldBoxSized,
+ * ray_bvh_intersection.rs:21-23; geometry/aabb.rs:286-303): min and size = max - min. */
+typedef struct MpBox {
+    float min[3];
+    float _pad0;
+    float size[3];
+    float _pad1;
+} MpBox; /* 32 B */
+
+/* InnerNode (mod.rs:33-38): child_bounds = RelativeBox8 {min:{x,y,z}, max:{x,y,z}} of u16x8
+ * (compressed_geometry.rs:59-63,117), then 8 links.  128 B = 8 x 16-byte loads. */
+typedef struct MpInnerNode {
+    uint16_t bounds[6][8]; /* [0..2] = min.x,min.y,min.z ; [3..5] = max.x,max.y,max.z ; [..][lane] */
+    uint32_t links[8];
+} MpInnerNode;
+
+/* RelativeTriangle8 (compressed_geometry.rs:147): 3 vertices x {x,y,z} x u16x8. 144 B = 9 x 16 B. */
+typedef struct MpTrianglePacket {
+    uint16_t v[3][3][8]; /* [vertex][axis][lane] */
+} MpTrianglePacket;
+
+/* TriangleShadingData (mod.rs:40-45) narrowed to u32: bit 31 of flags_material = flat_shading,
+ * low 31 bits = material.  Padding triangles hold {0,0,0,0} like the reference's Default. */
+typedef struct MpTriShading {
+    uint32_t v[3];
+    uint32_t flags_material;
+} MpTriShading;
+#define MP_TRI_FLAT 0x80000000u
+
+/* VertexShadingData (mod.rs:49-53). */
+typedef struct MpVertexShading {
+    float normal[3];
+    float _pad0;
+    float tex[3];
+    float _pad1;
+} MpVertexShading;
+
+typedef struct MpFlatBvh {
+    float bbox_min[3];
+    float bbox_max[3];
+    uint32_t root;        /* CompressedNodeLink */
+    uint32_t n_inner;
+    uint32_t n_packets;
+    uint32_t n_vertices;
+    uint32_t n_triangles; /* real (unpadded) triangles */
+    uint32_t _pad;
+    const MpInnerNode* inner;          /* [n_inner] */
+    const MpBox* inner_box;            /* [n_inner]   enclosing box each inner node is decoded against */
+    const MpTrianglePacket* packets;   /* [n_packets] */
+    const MpBox* packet_box;           /* [n_packets] enclosing box of the leaf the packet belongs to */
+    const MpTriShading* tri_shading;   /* [n_packets*8] indexed by packet*8+lane */
+    const MpVertexShading* vertices;   /* [n_vertices] */
+} MpFlatBvh;
+
+/* Host-side scene loading — replaces TriangleBvh::with_obj / build (building.rs:28-120).
+ * quad_mode: 0 = skip non-triangles like the reference (building.rs:43-46);
+ *            1 = fan-triangulate polygons (documented deviation, needed for data/cube.obj). */
+int mp_bvh_build_obj(const char* path, int quad_mode, MpFlatBvh** out);
+/* Build from an indexed mesh in memory (positions xyz, optional normals xyz (may be NULL → flat),
+ * triangles as 3 vertex indices).  Same builder as above. */
+int mp_bvh_build_mesh(const float* positions, const float* normals, uint32_t n_vertices,
+                      const uint32_t* triangles, uint64_t n_triangles, MpFlatBvh** out);
+/* builder: 0 = reference split (building.rs:238-345, O(G^3) agglomerative merge);
+ *          1 = median-split builder emitting the same node format (for large soups; not reference-pinned) */
+int mp_bvh_build_mesh_ex(const float* positions, const float* normals, uint32_t n_vertices,
+                         const uint32_t* triangles, uint64_t n_triangles, int builder, MpFlatBvh** out);
+int mp_bvh_free(MpFlatBvh* bvh);
+/* Structural statistics (node / packet counts, depth) — printing.rs:11-70 analogue, numbers only. */
+typedef struct MpBvhStats {
+    uint32_t n_inner, n_leaves, n_packets, n_triangles;
+    uint32_t max_depth, max_stack;
+    float mean_leaf_fill, mean_inner_fill;
+} MpBvhStats;
+int mp_bvh_stats(const MpFlatBvh* bvh, MpBvhStats* out);
+
+/* ---- camera: reference src/camera.rs ---- */
+typedef struct MpCamera { /* camera.rs:9-23 */
+    float center[3];
+    float forward[3];
+    float up[3];
+    float right[3];
+    float focus_distance;
+    float sensor_size;    /* metres */
+    int32_t sensor_is_width; /* SensorSize::Width / Height */
+    float focal_length;
+    float f_number;
+} MpCamera;
+typedef struct MpCameraSampler { /* camera.rs:26-39 */
+    float center[3];
+    float up[3];
+    float right[3];
+    float film_origin_offset[3];
+    float pixel_scale;
+    float lens_radius;
+    float lens_weight;
+} MpCameraSampler;
+int mp_camera_default(MpCamera* out);                                              /* camera.rs:42-52 */
+int mp_camera_look_at(MpCamera* cam, const float center[3], const float look_at[3],
+                      const float up[3]);                                           /* camera.rs:93-101 */
+int mp_camera_look_direction(MpCamera* cam, const float center[3], const float forward[3],
+                             const float up[3]);                                    /* camera.rs:104-116 */
+int mp_camera_build_sampler(const MpCamera* cam, uint32_t res_x, uint32_t res_y,
+                            MpCameraSampler* out);                                  /* camera.rs:123-146 */
+
+/* ---- screen tiling: reference src/screen_block.rs ---- */
+typedef struct MpTile { uint32_t min_x, min_y, max_x, max_y; } MpTile; /* ScreenBlock = AABB<Point2<u32>> */
+/* tile_ordering (screen_block.rs:46-81): tiles sorted by distance to centre + Exp noise.
+ * seed == 0 → noise drawn from the OS like the reference; otherwise deterministic.
+ * Writes up to cap tiles, returns the tile count in *out_n. */
+int mp_tile_ordering(uint32_t min_x, uint32_t min_y, uint32_t max_x, uint32_t max_y, uint32_t tile_size,
+                     uint64_t seed, MpTile* out, size_t cap, size_t* out_n);
+
+/* ---- device context ---- */
+typedef struct MpCtx MpCtx;
+
+typedef struct MpRay { /* geometry/mod.rs:34-42 */
+    float origin[3];
+    float direction[3];
+    float inv_direction[3];
+} MpRay; /* 36 B */
+typedef struct MpHit { /* LeafHitRecord (ray_bvh_intersection.rs:165-171) without the normal */
+    uint32_t tri;  /* packet*8+lane, MP_NO_HIT on miss */
+    float t, u, v;
+} MpHit; /* 16 B */
+
+#define MP_MODE_MEGAKERNEL 0u /* one thread per pixel runs the whole sample loop */
+#define MP_MODE_WAVEFRONT 1u  /* ray-gen → trace → shade → compact → … → film accumulate */
+#define MP_ORDER_REFERENCE 0u /* exact LIFO / lane order of ray_bvh_intersection.rs:39-64,161 (bit-exact gate) */
+#define MP_ORDER_NEAR_FIRST 1u /* children pushed far→near; not bit-pinned, mismatches are reported */
+
+typedef struct MpRenderParams {
+    uint32_t sample_count;   /* RenderSettings::sample_count for this call (renderer/mod.rs:9) */
+    uint32_t sample_base;    /* index of the first sample (spp split across GPUs / progressive passes) */
+    uint32_t max_bounces;    /* 0 = the reference shader (worker.rs:57-64); >0 = extension integrator */
+    uint32_t mode;           /* MP_MODE_* */
+    uint32_t order;          /* MP_ORDER_* */
+    uint32_t tile_size;      /* RenderSettings::tile_size: upper bound of every tile's width and height */
+    uint64_t seed;
+} MpRenderParams;
+
+typedef struct MpCounters {
+    uint64_t rays;          /* ray segments traced (camera + bounce + shadow) */
+    uint64_t camera_rays;
+    uint64_t shadow_rays;
+    uint64_t inner_visits;  /* inner nodes decoded  (128 B each) */
+    uint64_t packet_visits; /* triangle packets tested (144 B each) */
+    uint64_t leaf_visits;
+    uint64_t launches;      /* kernels launched by this library */
+} MpCounters;
+
+const char* mp_last_error(void);
+int mp_device_count(int* out);
+int mp_ctx_create(int device, MpCtx** out);
+int mp_ctx_destroy(MpCtx* ctx);
+/* Run on a caller-owned CUDA stream (cudaStream_t as void*); NULL → the context's own stream. */
+int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream);
+int mp_ctx_sync(MpCtx* ctx);
+/* Count traversal work (adds a few atomics per warp); off by default. */
+int mp_ctx_enable_counters(MpCtx* ctx, int on);
+int mp_counters(MpCtx* ctx, MpCounters* out);
+int mp_counters_reset(MpCtx* ctx);
+/* Device time (ms, CUDA events on the launching stream) of the last render/trace call's kernels. */
+int mp_last_device_ms(MpCtx* ctx, float* out_ms);
+
+/* Scene<TriangleBvh> → device (borrowed host arrays are copied; caller keeps ownership). */
+int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* bvh);
+/* CameraSampler for the render (camera.build_sampler(resolution), machinery.rs:65). */
+int mp_camera_set(MpCtx* ctx, const MpCameraSampler* sampler);
+
+/* Film = f32x4 accumulator per pixel (the `pixel_sum` of worker.rs:40-43 kept on the device). */
+int mp_film_create(MpCtx* ctx, uint32_t width, uint32_t height);
+/* Use caller-owned device memory (width*height*4 floats) as the film, e.g. a tensor that a collective reduces. */
+int mp_film_bind_external(MpCtx* ctx, void* device_ptr, uint32_t width, uint32_t height);
+int mp_film_clear(MpCtx* ctx);
+int mp_film_device_ptr(MpCtx* ctx, void** out);
+
+/* Worker::render_tile for n tiles at once (worker.rs:32-49): accumulates sample_count samples per pixel
+ * into the film, sequentially per pixel in sample order.  Asynchronous on the context's stream. */
+int mp_render_tiles(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, const MpRenderParams* params);
+/* pixel_sum * (1/spp) then color_to_image (worker.rs:44,69-76) for the whole film → host RGBA8. Synchronises. */
+int mp_film_resolve_rgba8(MpCtx* ctx, uint32_t spp_total, uint8_t* host_out);
+/* Same, tiles only, into a tile-packed host buffer is not needed: the full image is the unit of transfer. */
+int mp_film_read_f32(MpCtx* ctx, float* host_out);
+
+/* Object::intersect on caller rays (scene/mod.rs:7-10; ray_bvh_intersection.rs:26-64) — the bit-exactness gate. */
+int mp_trace_rays(MpCtx* ctx, const MpRay* host_rays, uint64_t n, uint32_t order, MpHit* host_out);
+/* Device-resident variant (pointers from mp_dev_alloc or any CUDA allocation). Asynchronous. */
+int mp_trace_rays_device(MpCtx* ctx, const MpRay* dev_rays, uint64_t n, uint32_t order, MpHit* dev_out);
+/* CameraSampler::sample_ray (camera.rs:176-191) for every (pixel, sample) of the tiles, in
+ * tile → row-major pixel → sample order; writes n_pixels*sample_count rays to the host. */
+int mp_generate_rays(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, const MpRenderParams* params,
+                     MpRay* host_out, uint64_t cap, uint64_t* out_n);
+
+/* Raw device memory helpers for harnesses that keep inputs resident in HBM. */
+int mp_dev_alloc(MpCtx* ctx, size_t bytes, void** out);
+int mp_dev_free(MpCtx* ctx, void* ptr);
+int mp_dev_upload(MpCtx* ctx, void* dev_dst, const void* host_src, size_t bytes);
+int mp_dev_download(MpCtx* ctx, void* host_dst, const void* dev_src, size_t bytes);
+int mp_host_alloc_pinned(size_t bytes, void** out);
+int mp_host_free_pinned(void* ptr);
+
+/* ---- render(): reference src/renderer/machinery.rs:20-123 ---- */
+typedef struct MpRenderSettings { /* renderer/mod.rs:7-13 + extension fields with reference-preserving defaults */
+    uint32_t tile_size;
+    uint32_t sample_count;
+    uint32_t resolution_x, resolution_y;
+    uint32_t max_bounces; /* 0 → reference behaviour */
+    uint32_t mode;        /* MP_MODE_* */
+    uint32_t order;       /* MP_ORDER_* */
+    uint32_t tiles_per_batch; /* 0 → default */
+    uint64_t seed;        /* 0 → OS-random like SmallRng::from_os_rng (worker.rs:25) */
+} MpRenderSettings;
+typedef struct MpProgressSnapshot { size_t finished, total; } MpProgressSnapshot; /* machinery.rs:180-183 */
+typedef void (*MpStartedTileFn)(void* user, MpTile tile);
+typedef void (*MpFinishedTileFn)(void* user, MpTile tile, MpProgressSnapshot progress);
+typedef struct MpRenderProgress MpRenderProgress;
+
+/* Starts rendering on background worker threads (one per device in `devices`) and returns immediately.
+ * Callbacks fire from worker threads: started before a tile renders, finished after its pixels are in the image. */
+int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSettings* settings,
+              const int* devices, int n_devices,
+              MpStartedTileFn started, MpFinishedTileFn finished, void* user, MpRenderProgress** out);
+int mp_progress_snapshot(MpRenderProgress* p, MpProgressSnapshot* out); /* machinery.rs:133-142 */
+int mp_progress_is_finished(MpRenderProgress* p, int* out);             /* :144-146 */
+int mp_progress_elapsed_ms(MpRenderProgress* p, double* out);           /* :150-157 */
+int mp_progress_abort(MpRenderProgress* p);                             /* :161-165 */
+int mp_progress_wait(MpRenderProgress* p);                              /* :169-173 */
+/* Copies the RGBA8 image (w*h*4) under the image lock (:175-177). */
+int mp_progress_image(MpRenderProgress* p, uint8_t* host_out, size_t cap);
+int mp_progress_free(MpRenderProgress* p);
+
+/* Cross-process dynamic tile queue (the AtomicUsize of machinery.rs:43,205-209 shared by the ranks of one box). */
+typedef struct MpTileQueue MpTileQueue;
+int mp_tileq_open(const char* name, int create, MpTileQueue** out);
+int mp_tileq_reset(MpTileQueue* q);
+int mp_tileq_next(MpTileQueue* q, uint64_t batch, uint64_t* out_first); /* fetch_add(batch) */
+int mp_tileq_close(MpTileQueue* q, int unlink);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MINIPATH_B200_H */
