@@ -1,0 +1,31 @@
+# Builds the product library (CUDA, sm_100a only) and the CPU oracle (test infrastructure).
+NVCC ?= /usr/local/cuda/bin/nvcc
+CXX ?= g++
+CS := minipath_b200/csrc
+LIB := minipath_b200/libminipath_b200.so
+ORACLE := oracle/liboracle.so
+
+HOST_FLAGS := -O2 -std=c++17 -fPIC -ffp-contract=off -Wall -Wextra -Wno-unused-parameter
+NVCC_FLAGS := -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false -prec-div=true -prec-sqrt=true \
+              -Xcompiler -fPIC,-ffp-contract=off -Xptxas -v
+
+all: $(LIB) $(ORACLE)
+
+$(CS)/host_bvh.o: $(CS)/host_bvh.cpp $(CS)/host_bvh_build.inc $(CS)/host_common.h include/minipath_b200.h
+	$(CXX) $(HOST_FLAGS) -c $< -o $@
+$(CS)/host_camera.o: $(CS)/host_camera.cpp $(CS)/host_common.h include/minipath_b200.h
+	$(CXX) $(HOST_FLAGS) -c $< -o $@
+$(CS)/host_render.o: $(CS)/host_render.cpp $(CS)/host_common.h include/minipath_b200.h
+	$(CXX) $(HOST_FLAGS) -c $< -o $@
+$(CS)/context.o: $(CS)/context.cu $(CS)/context_render.inc $(CS)/kernels.cuh $(CS)/wavefront.cuh $(CS)/trace.cuh $(CS)/device_math.cuh include/minipath_b200.h
+	$(NVCC) $(NVCC_FLAGS) -c $< -o $@ 2> $(CS)/ptxas.log || (cat $(CS)/ptxas.log; false)
+
+$(LIB): $(CS)/host_bvh.o $(CS)/host_camera.o $(CS)/host_render.o $(CS)/context.o
+	$(NVCC) -shared -o $@ $^ -lpthread -lrt -cudart static
+
+$(ORACLE): oracle/oracle.cpp oracle/oracle_trace.inc oracle/oracle_render.inc oracle/oracle.h include/minipath_b200.h
+	$(CXX) -O2 -std=c++17 -fPIC -shared -mavx2 -mfma -ffp-contract=off -Wall -o $@ oracle/oracle.cpp -lpthread
+
+clean:
+	rm -f $(CS)/*.o $(CS)/ptxas.log $(LIB) $(ORACLE)
+.PHONY: all clean

@@ -229,7 +229,10 @@ int mp_film_device_ptr(MpCtx* ctx, void** out);
 int mp_render_tiles(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, const MpRenderParams* params);
 /* pixel_sum * (1/spp) then color_to_image (worker.rs:44,69-76) for the whole film → host RGBA8. Synchronises. */
 int mp_film_resolve_rgba8(MpCtx* ctx, uint32_t spp_total, uint8_t* host_out);
-/* Same, tiles only, into a tile-packed host buffer is not needed: the full image is the unit of transfer. */
+/* Same for n tiles only, into a tile-packed host buffer [n_tiles][tile_size][tile_size] RGBA8 — the worker's
+ * `buffer` of machinery.rs:66-67 for a whole batch; only the first (w x h) of each tile slot is written. Synchronises. */
+int mp_film_resolve_tiles_rgba8(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, uint32_t tile_size, uint32_t spp_total,
+                                uint8_t* host_out);
 int mp_film_read_f32(MpCtx* ctx, float* host_out);
 
 /* Object::intersect on caller rays (scene/mod.rs:7-10; ray_bvh_intersection.rs:26-64) — the bit-exactness gate. */

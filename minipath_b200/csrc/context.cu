@@ -1,0 +1,312 @@
+// Device context and the C ABI around the kernels (include/minipath_b200.h).
+// nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -prec-div=true -prec-sqrt=true -lineinfo
+#include <cstring>
+#include <vector>
+
+#include "host_common.h"
+#include "kernels.cuh"
+#include "wavefront.cuh"
+
+using namespace mp;
+
+#define CK(call)                                                                                                  \
+    do {                                                                                                          \
+        cudaError_t _e = (call);                                                                                  \
+        if (_e != cudaSuccess) return fail(MP_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+struct MpCtx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    bool count_visits = false;
+    uint64_t launches = 0;
+
+    // scene
+    void* d_scene_blob = nullptr;
+    mpd::Scene scene{};
+    bool has_scene = false;
+    uint32_t max_stack = 0;
+    // camera
+    mpd::Camera cam{};
+    bool has_cam = false;
+    // film
+    float4* film = nullptr;
+    bool film_owned = false;
+    uint32_t width = 0, height = 0;
+    uint32_t* d_rgba8 = nullptr;
+    uint32_t* d_tile_out = nullptr;
+    size_t tile_out_cap = 0;
+    // counters
+    mpd::DevCounters* d_counters = nullptr;
+    // tile staging
+    MpTile* d_tiles = nullptr;
+    size_t tiles_cap = 0;
+    MpTile* h_tiles_pinned = nullptr;
+    // wavefront state
+    mpd::WavefrontBuffers wf{};
+};
+
+static int use_device(MpCtx* ctx) {
+    if (!ctx) return fail(MP_EINVAL, "null context");
+    CK(cudaSetDevice(ctx->device));
+    return MP_OK;
+}
+
+static uint32_t seed_hash(uint64_t seed) {
+    auto h = [](uint32_t v) {
+        uint32_t s = v * 747796405u + 2891336453u;
+        uint32_t w = ((s >> ((s >> 28) + 4u)) ^ s) * 277803737u;
+        return (w >> 22) ^ w;
+    };
+    return h((uint32_t)seed ^ h((uint32_t)(seed >> 32)));
+}
+
+static int stage_tiles(MpCtx* ctx, const MpTile* tiles, uint32_t n) {
+    if (n > ctx->tiles_cap) {
+        if (ctx->d_tiles) CK(cudaFree(ctx->d_tiles));
+        if (ctx->h_tiles_pinned) CK(cudaFreeHost(ctx->h_tiles_pinned));
+        ctx->d_tiles = nullptr, ctx->h_tiles_pinned = nullptr;
+        size_t cap = std::max<size_t>(n, 1024);
+        CK(cudaMalloc(&ctx->d_tiles, cap * sizeof(MpTile)));
+        CK(cudaMallocHost(&ctx->h_tiles_pinned, cap * sizeof(MpTile)));
+        ctx->tiles_cap = cap;
+    } else {
+        // the pinned staging buffer may still be in flight from the previous call on this stream
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    memcpy(ctx->h_tiles_pinned, tiles, n * sizeof(MpTile));
+    CK(cudaMemcpyAsync(ctx->d_tiles, ctx->h_tiles_pinned, n * sizeof(MpTile), cudaMemcpyHostToDevice, ctx->stream));
+    return MP_OK;
+}
+
+static mpd::TileMap make_tile_map(MpCtx* ctx, uint32_t n_tiles, uint32_t tile_size) {
+    mpd::TileMap tm;
+    tm.tiles = ctx->d_tiles;
+    tm.n_tiles = n_tiles;
+    tm.mt_x = (tile_size + 7) / 8;
+    tm.threads_per_tile = tm.mt_x * ((tile_size + 3) / 4) * 32;
+    return tm;
+}
+
+static int check_tiles(MpCtx* ctx, const MpTile* tiles, uint32_t n, uint32_t tile_size, bool need_film) {
+    if (!tiles && n) return fail(MP_EINVAL, "null tiles");
+    if (tile_size == 0) return fail(MP_EINVAL, "tile_size must be non-zero");
+    for (uint32_t i = 0; i < n; ++i) {
+        const MpTile& t = tiles[i];
+        if (t.max_x < t.min_x || t.max_y < t.min_y || t.max_x - t.min_x > tile_size || t.max_y - t.min_y > tile_size)
+            return fail(MP_EINVAL, "tile %u larger than tile_size %u", i, tile_size);
+        if (need_film && (t.max_x > ctx->width || t.max_y > ctx->height)) return fail(MP_EINVAL, "tile %u outside the %ux%u film", i, ctx->width, ctx->height);
+    }
+    return MP_OK;
+}
+
+extern "C" {
+
+int mp_device_count(int* out) {
+    if (!out) return fail(MP_EINVAL, "null out");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        *out = 0;
+        return fail(MP_ENODEVICE, "no CUDA device: %s", cudaGetErrorString(e));
+    }
+    *out = n;
+    return MP_OK;
+}
+
+int mp_ctx_create(int device, MpCtx** out) {
+    if (!out) return fail(MP_EINVAL, "null out");
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) return fail(MP_ENODEVICE, "no CUDA device available; this library has no CPU fallback");
+    if (device < 0 || device >= n) return fail(MP_EINVAL, "device %d out of range (have %d)", device, n);
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(MP_ENODEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    MpCtx* ctx = new MpCtx();
+    ctx->device = device;
+    CK(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+    ctx->stream = ctx->own_stream;
+    CK(cudaEventCreate(&ctx->ev0));
+    CK(cudaEventCreate(&ctx->ev1));
+    CK(cudaMalloc(&ctx->d_counters, sizeof(mpd::DevCounters)));
+    CK(cudaMemset(ctx->d_counters, 0, sizeof(mpd::DevCounters)));
+    *out = ctx;
+    return MP_OK;
+}
+
+int mp_ctx_destroy(MpCtx* ctx) {
+    if (!ctx) return MP_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    mpd::wavefront_free(ctx->wf);
+    if (ctx->d_scene_blob) cudaFree(ctx->d_scene_blob);
+    if (ctx->film && ctx->film_owned) cudaFree(ctx->film);
+    if (ctx->d_rgba8) cudaFree(ctx->d_rgba8);
+    if (ctx->d_tile_out) cudaFree(ctx->d_tile_out);
+    if (ctx->d_counters) cudaFree(ctx->d_counters);
+    if (ctx->d_tiles) cudaFree(ctx->d_tiles);
+    if (ctx->h_tiles_pinned) cudaFreeHost(ctx->h_tiles_pinned);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+    return MP_OK;
+}
+
+int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream) {
+    if (int rc = use_device(ctx)) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    return MP_OK;
+}
+
+int mp_ctx_sync(MpCtx* ctx) {
+    if (int rc = use_device(ctx)) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MP_OK;
+}
+
+int mp_ctx_enable_counters(MpCtx* ctx, int on) {
+    if (!ctx) return fail(MP_EINVAL, "null context");
+    ctx->count_visits = on != 0;
+    return MP_OK;
+}
+
+int mp_counters(MpCtx* ctx, MpCounters* out) {
+    if (int rc = use_device(ctx)) return rc;
+    if (!out) return fail(MP_EINVAL, "null out");
+    mpd::DevCounters h;
+    CK(cudaMemcpyAsync(&h, ctx->d_counters, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    out->rays = h.rays, out->camera_rays = h.camera_rays, out->shadow_rays = h.shadow_rays;
+    out->inner_visits = h.inner_visits, out->packet_visits = h.packet_visits, out->leaf_visits = h.leaf_visits;
+    out->launches = ctx->launches;
+    return MP_OK;
+}
+
+int mp_counters_reset(MpCtx* ctx) {
+    if (int rc = use_device(ctx)) return rc;
+    CK(cudaMemsetAsync(ctx->d_counters, 0, sizeof(mpd::DevCounters), ctx->stream));
+    ctx->launches = 0;
+    return MP_OK;
+}
+
+int mp_last_device_ms(MpCtx* ctx, float* out_ms) {
+    if (int rc = use_device(ctx)) return rc;
+    if (!out_ms) return fail(MP_EINVAL, "null out");
+    if (!ctx->timed) return fail(MP_ESTATE, "no render or trace call has been issued yet");
+    CK(cudaEventSynchronize(ctx->ev1));
+    CK(cudaEventElapsedTime(out_ms, ctx->ev0, ctx->ev1));
+    return MP_OK;
+}
+
+int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
+    if (int rc = use_device(ctx)) return rc;
+    if (!b || !b->packets || !b->packet_box || !b->tri_shading || !b->vertices || (b->n_inner && (!b->inner || !b->inner_box)))
+        return fail(MP_EINVAL, "incomplete MpFlatBvh");
+    if (b->n_packets == 0) return fail(MP_EINVAL, "scene has no triangle packets");
+    MpBvhStats st;
+    if (int rc = mp_bvh_stats(b, &st)) return rc;
+    if (st.max_stack > MPD_STACK_MAX) return fail(MP_EINVAL, "BVH depth %u needs a %u-entry stack (limit %d)", st.max_depth, st.max_stack, MPD_STACK_MAX);
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->d_scene_blob) CK(cudaFree(ctx->d_scene_blob));
+    ctx->d_scene_blob = nullptr;
+    // one allocation, every array 256-byte aligned
+    auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    const size_t s_inner = al((size_t)b->n_inner * sizeof(MpInnerNode)), s_ibox = al((size_t)b->n_inner * sizeof(MpBox));
+    const size_t s_pack = al((size_t)b->n_packets * sizeof(MpTrianglePacket)), s_pbox = al((size_t)b->n_packets * sizeof(MpBox));
+    const size_t s_sh = al((size_t)b->n_packets * 8 * sizeof(MpTriShading)), s_v = al((size_t)b->n_vertices * sizeof(MpVertexShading));
+    const size_t total = s_inner + s_ibox + s_pack + s_pbox + s_sh + s_v + 256;
+    CK(cudaMalloc(&ctx->d_scene_blob, total));
+    char* p = (char*)ctx->d_scene_blob;
+    auto up = [&](const void* src, size_t bytes, size_t slot) -> const void* {
+        const void* dst = p;
+        if (bytes) cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, ctx->stream);
+        p += slot;
+        return dst;
+    };
+    ctx->scene.inner = (const uint4*)up(b->inner, (size_t)b->n_inner * sizeof(MpInnerNode), s_inner);
+    ctx->scene.inner_box = (const float4*)up(b->inner_box, (size_t)b->n_inner * sizeof(MpBox), s_ibox);
+    ctx->scene.packets = (const uint4*)up(b->packets, (size_t)b->n_packets * sizeof(MpTrianglePacket), s_pack);
+    ctx->scene.packet_box = (const float4*)up(b->packet_box, (size_t)b->n_packets * sizeof(MpBox), s_pbox);
+    ctx->scene.tri_shading = (const uint4*)up(b->tri_shading, (size_t)b->n_packets * 8 * sizeof(MpTriShading), s_sh);
+    ctx->scene.vertices = (const float4*)up(b->vertices, (size_t)b->n_vertices * sizeof(MpVertexShading), s_v);
+    ctx->scene.root = b->root;
+    {  // extension integrator epsilon: 1e-4 * |bbox size|, same unfused arithmetic as the oracle
+        V3 s = v3(b->bbox_max[0], b->bbox_max[1], b->bbox_max[2]) - v3(b->bbox_min[0], b->bbox_min[1], b->bbox_min[2]);
+        ctx->scene.eps = 1e-4f * std::sqrt(dot(s, s));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaGetLastError());
+    ctx->max_stack = st.max_stack;
+    ctx->has_scene = true;
+    return MP_OK;
+}
+
+int mp_camera_set(MpCtx* ctx, const MpCameraSampler* s) {
+    if (!ctx || !s) return fail(MP_EINVAL, "null argument");
+    ctx->cam.center = mpd::F3{s->center[0], s->center[1], s->center[2]};
+    ctx->cam.up = mpd::F3{s->up[0], s->up[1], s->up[2]};
+    ctx->cam.right = mpd::F3{s->right[0], s->right[1], s->right[2]};
+    ctx->cam.film_origin_offset = mpd::F3{s->film_origin_offset[0], s->film_origin_offset[1], s->film_origin_offset[2]};
+    ctx->cam.pixel_scale = s->pixel_scale;
+    ctx->cam.lens_radius = s->lens_radius;
+    ctx->cam.lens_weight = s->lens_weight;
+    ctx->has_cam = true;
+    return MP_OK;
+}
+
+static int film_release(MpCtx* ctx) {
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->film && ctx->film_owned) CK(cudaFree(ctx->film));
+    if (ctx->d_rgba8) CK(cudaFree(ctx->d_rgba8));
+    ctx->film = nullptr, ctx->d_rgba8 = nullptr;
+    return MP_OK;
+}
+
+int mp_film_create(MpCtx* ctx, uint32_t width, uint32_t height) {
+    if (int rc = use_device(ctx)) return rc;
+    if (width == 0 || height == 0 || (uint64_t)width * height > 0x7fffffffull) return fail(MP_EINVAL, "bad film size %ux%u", width, height);
+    if (int rc = film_release(ctx)) return rc;
+    const size_t n = (size_t)width * height;
+    CK(cudaMalloc(&ctx->film, n * sizeof(float4)));
+    CK(cudaMalloc(&ctx->d_rgba8, n * sizeof(uint32_t)));
+    CK(cudaMemsetAsync(ctx->film, 0, n * sizeof(float4), ctx->stream));
+    ctx->film_owned = true;
+    ctx->width = width, ctx->height = height;
+    return MP_OK;
+}
+
+int mp_film_bind_external(MpCtx* ctx, void* device_ptr, uint32_t width, uint32_t height) {
+    if (int rc = use_device(ctx)) return rc;
+    if (!device_ptr || ((uintptr_t)device_ptr & 15)) return fail(MP_EINVAL, "film pointer must be a 16-byte aligned device pointer");
+    if (width == 0 || height == 0 || (uint64_t)width * height > 0x7fffffffull) return fail(MP_EINVAL, "bad film size %ux%u", width, height);
+    if (int rc = film_release(ctx)) return rc;
+    ctx->film = (float4*)device_ptr;
+    ctx->film_owned = false;
+    CK(cudaMalloc(&ctx->d_rgba8, (size_t)width * height * sizeof(uint32_t)));
+    ctx->width = width, ctx->height = height;
+    return MP_OK;
+}
+
+int mp_film_clear(MpCtx* ctx) {
+    if (int rc = use_device(ctx)) return rc;
+    if (!ctx->film) return fail(MP_ESTATE, "no film");
+    CK(cudaMemsetAsync(ctx->film, 0, (size_t)ctx->width * ctx->height * sizeof(float4), ctx->stream));
+    return MP_OK;
+}
+
+int mp_film_device_ptr(MpCtx* ctx, void** out) {
+    if (!ctx || !out) return fail(MP_EINVAL, "null argument");
+    if (!ctx->film) return fail(MP_ESTATE, "no film");
+    *out = ctx->film;
+    return MP_OK;
+}
+
+}  // extern "C"
+
+#include "context_render.inc"

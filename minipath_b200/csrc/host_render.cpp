@@ -1,0 +1,220 @@
+// render(): the reference's tile scheduler (src/renderer/machinery.rs:20-210) with GPUs as the workers.
+// One host thread per device pulls batches of tiles from one shared atomic counter (next_tile_index,
+// machinery.rs:43,205-209), renders them with mp_render_tiles, resolves the batch to RGBA8 and copies it into the
+// shared image under its mutex (machinery.rs:78-89), firing the reference's two callbacks from the worker thread.
+#include <atomic>
+#include <chrono>
+#include <cstring>
+#include <mutex>
+#include <random>
+#include <thread>
+#include <vector>
+
+#include "host_common.h"
+
+using namespace mp;
+
+struct MpRenderProgress {
+    // RenderState (machinery.rs:191-203)
+    MpRenderSettings settings{};
+    MpCameraSampler sampler{};
+    const MpFlatBvh* scene = nullptr;
+    std::mutex image_mutex;
+    std::vector<uint8_t> image;  // RGBA8, w*h*4
+    std::vector<MpTile> tile_ordering;
+    std::atomic<size_t> next_tile_index{0};
+    std::chrono::steady_clock::time_point start_time;
+    std::mutex end_mutex;
+    size_t workers_done = 0;
+    bool has_end = false;
+    std::chrono::steady_clock::duration end_elapsed{};
+    // RenderProgress (machinery.rs:125-129)
+    size_t worker_count = 0;
+    size_t batch = 1;
+    std::vector<std::thread> threads;
+    std::atomic<size_t> threads_finished{0};
+    MpStartedTileFn started = nullptr;
+    MpFinishedTileFn finished = nullptr;
+    void* user = nullptr;
+    std::mutex error_mutex;
+    std::string error;
+    int error_code = MP_OK;
+};
+
+static void worker_fail(MpRenderProgress* p, int code) {
+    std::lock_guard<std::mutex> g(p->error_mutex);
+    if (p->error_code == MP_OK) {
+        p->error_code = code;
+        p->error = mp_last_error();
+    }
+    p->next_tile_index.store(p->tile_ordering.size(), std::memory_order_release);  // stop the other workers too
+}
+
+static void worker_main(MpRenderProgress* p, int device) {
+    const MpRenderSettings& s = p->settings;
+    const size_t total = p->tile_ordering.size();
+    MpCtx* ctx = nullptr;
+    int rc = mp_ctx_create(device, &ctx);
+    if (!rc) rc = mp_scene_upload(ctx, p->scene);
+    if (!rc) rc = mp_camera_set(ctx, &p->sampler);  // camera.build_sampler(settings.resolution) (machinery.rs:65)
+    if (!rc) rc = mp_film_create(ctx, s.resolution_x, s.resolution_y);
+    std::vector<uint8_t> buffer(p->batch * (size_t)s.tile_size * s.tile_size * 4);  // tile buffers (machinery.rs:66-67)
+    MpRenderParams params{};
+    params.sample_count = s.sample_count;
+    params.sample_base = 0;
+    params.max_bounces = s.max_bounces;
+    params.mode = s.mode;
+    params.order = s.order;
+    params.tile_size = s.tile_size;
+    params.seed = s.seed;
+    if (rc) worker_fail(p, rc);
+
+    while (!rc) {
+        const size_t first = p->next_tile_index.fetch_add(p->batch, std::memory_order_acq_rel);  // get_next_tile
+        if (first >= total) break;
+        const size_t n = std::min(p->batch, total - first);
+        const MpTile* tiles = &p->tile_ordering[first];
+        if (p->started)
+            for (size_t i = 0; i < n; ++i) p->started(p->user, tiles[i]);
+        rc = mp_render_tiles(ctx, tiles, (uint32_t)n, &params);  // worker.render_tile (machinery.rs:77)
+        if (!rc) rc = mp_film_resolve_tiles_rgba8(ctx, tiles, (uint32_t)n, s.tile_size, s.sample_count, buffer.data());
+        if (rc) {
+            worker_fail(p, rc);
+            break;
+        }
+        {  // image.lock().copy_from(buffer.view(0,0,w,h), tile.min) (machinery.rs:78-89)
+            std::lock_guard<std::mutex> g(p->image_mutex);
+            for (size_t i = 0; i < n; ++i) {
+                const MpTile& t = tiles[i];
+                const size_t w = t.max_x - t.min_x;
+                for (uint32_t y = t.min_y; y < t.max_y; ++y)
+                    memcpy(&p->image[((size_t)y * s.resolution_x + t.min_x) * 4],
+                           &buffer[((i * s.tile_size + (y - t.min_y)) * s.tile_size) * 4], w * 4);
+            }
+        }
+        if (p->finished) {
+            const size_t next_id = std::min(p->next_tile_index.load(std::memory_order_acquire), total + p->worker_count * p->batch);
+            const size_t in_flight = p->worker_count * p->batch;
+            MpProgressSnapshot snap{next_id > in_flight ? std::min(next_id - in_flight, total) : 0, total};  // saturating_sub (machinery.rs:96)
+            for (size_t i = 0; i < n; ++i) p->finished(p->user, tiles[i], snap);
+        }
+    }
+    if (ctx) mp_ctx_destroy(ctx);
+    {
+        auto elapsed = std::chrono::steady_clock::now() - p->start_time;  // machinery.rs:107-113
+        std::lock_guard<std::mutex> g(p->end_mutex);
+        p->workers_done += 1;
+        if (p->workers_done == p->worker_count) {
+            p->has_end = true;
+            p->end_elapsed = elapsed;
+        }
+    }
+    p->threads_finished.fetch_add(1, std::memory_order_release);
+}
+
+extern "C" {
+
+int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSettings* settings, const int* devices, int n_devices,
+              MpStartedTileFn started, MpFinishedTileFn finished, void* user, MpRenderProgress** out) {
+    if (!scene || !camera || !settings || !out) return fail(MP_EINVAL, "null argument");
+    if (settings->tile_size == 0 || settings->sample_count == 0) return fail(MP_EINVAL, "tile_size and sample_count must be non-zero (NonZeroU32)");
+    if (settings->resolution_x == 0 || settings->resolution_y == 0) return fail(MP_EINVAL, "empty resolution");
+    int have = 0;
+    if (int rc = mp_device_count(&have)) return rc;
+    if (have == 0) return fail(MP_ENODEVICE, "no CUDA device available; this library has no CPU fallback");
+    std::vector<int> devs;
+    if (devices && n_devices > 0)
+        devs.assign(devices, devices + n_devices);
+    else
+        for (int i = 0; i < have; ++i) devs.push_back(i);  // one worker per device, like one per core (machinery.rs:31-32)
+    for (int d : devs)
+        if (d < 0 || d >= have) return fail(MP_EINVAL, "device %d out of range (have %d)", d, have);
+
+    MpRenderProgress* p = new MpRenderProgress();
+    p->settings = *settings;
+    if (p->settings.seed == 0) {  // SmallRng::from_os_rng (worker.rs:25)
+        std::random_device rd;
+        p->settings.seed = ((uint64_t)rd() << 32) | rd();
+        if (p->settings.seed == 0) p->settings.seed = 1;
+    }
+    p->scene = scene;
+    if (int rc = mp_camera_build_sampler(camera, settings->resolution_x, settings->resolution_y, &p->sampler)) {
+        delete p;
+        return rc;
+    }
+    p->image.assign((size_t)settings->resolution_x * settings->resolution_y * 4, 0);  // RgbaImage::new (machinery.rs:34)
+    size_t n_tiles = 0;
+    mp_tile_ordering(0, 0, settings->resolution_x, settings->resolution_y, settings->tile_size, 0, nullptr, 0, &n_tiles);
+    p->tile_ordering.resize(n_tiles);
+    if (int rc = mp_tile_ordering(0, 0, settings->resolution_x, settings->resolution_y, settings->tile_size, 0, p->tile_ordering.data(),
+                                  n_tiles, &n_tiles)) {
+        delete p;
+        return rc;
+    }
+    p->worker_count = devs.size();
+    p->batch = settings->tiles_per_batch ? settings->tiles_per_batch : 32;
+    p->started = started, p->finished = finished, p->user = user;
+    p->start_time = std::chrono::steady_clock::now();
+    try {
+        for (int d : devs) p->threads.emplace_back(worker_main, p, d);
+    } catch (const std::exception& e) {  // anyhow::Result from thread spawn (machinery.rs:116)
+        p->next_tile_index.store(n_tiles);
+        for (auto& t : p->threads) t.join();
+        delete p;
+        return fail(MP_ENOMEM, "thread spawn failed: %s", e.what());
+    }
+    *out = p;
+    return MP_OK;
+}
+
+int mp_progress_snapshot(MpRenderProgress* p, MpProgressSnapshot* out) {  // machinery.rs:133-142
+    if (!p || !out) return fail(MP_EINVAL, "null argument");
+    const size_t total = p->tile_ordering.size(), in_flight = p->worker_count * p->batch;
+    const size_t next_id = p->next_tile_index.load(std::memory_order_acquire);
+    out->finished = next_id > in_flight ? std::min(next_id - in_flight, total) : 0;
+    out->total = total;
+    return MP_OK;
+}
+int mp_progress_is_finished(MpRenderProgress* p, int* out) {  // machinery.rs:144-146
+    if (!p || !out) return fail(MP_EINVAL, "null argument");
+    *out = p->threads_finished.load(std::memory_order_acquire) == p->worker_count;
+    return MP_OK;
+}
+int mp_progress_elapsed_ms(MpRenderProgress* p, double* out) {  // machinery.rs:150-157
+    if (!p || !out) return fail(MP_EINVAL, "null argument");
+    std::lock_guard<std::mutex> g(p->end_mutex);
+    auto d = p->has_end ? p->end_elapsed : (std::chrono::steady_clock::now() - p->start_time);
+    *out = std::chrono::duration<double, std::milli>(d).count();
+    return MP_OK;
+}
+int mp_progress_abort(MpRenderProgress* p) {  // machinery.rs:161-165
+    if (!p) return fail(MP_EINVAL, "null argument");
+    p->next_tile_index.store(p->tile_ordering.size(), std::memory_order_release);
+    return MP_OK;
+}
+int mp_progress_wait(MpRenderProgress* p) {  // machinery.rs:169-173
+    if (!p) return fail(MP_EINVAL, "null argument");
+    for (auto& t : p->threads)
+        if (t.joinable()) t.join();
+    p->threads.clear();
+    std::lock_guard<std::mutex> g(p->error_mutex);
+    if (p->error_code != MP_OK) return fail(p->error_code, "render worker failed: %s", p->error.c_str());
+    return MP_OK;
+}
+int mp_progress_image(MpRenderProgress* p, uint8_t* host_out, size_t cap) {  // machinery.rs:175-177
+    if (!p || !host_out) return fail(MP_EINVAL, "null argument");
+    std::lock_guard<std::mutex> g(p->image_mutex);
+    if (cap < p->image.size()) return fail(MP_EINVAL, "image buffer too small: %zu < %zu", cap, p->image.size());
+    memcpy(host_out, p->image.data(), p->image.size());
+    return MP_OK;
+}
+int mp_progress_free(MpRenderProgress* p) {
+    if (!p) return MP_OK;
+    mp_progress_abort(p);
+    for (auto& t : p->threads)
+        if (t.joinable()) t.join();
+    delete p;
+    return MP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,205 @@
+// Kernels of the trace path: primary-ray dump, caller-ray trace (gate), the per-pixel megakernel and film resolve.
+// The wavefront pipeline lives in wavefront.cuh.
+#pragma once
+#include "trace.cuh"
+
+namespace mpd {
+
+// Extension integrator constants (max_bounces > 0; the reference defines no behaviour there — SURVEY A.7)
+#define EXT_ALBEDO 0.7f
+#define EXT_ENV 1.0f
+#define EXT_SUN_E 1.0f
+#define EXT_SUN_X 0.25916052f
+#define EXT_SUN_Y 0.86386842f
+#define EXT_SUN_Z 0.43193421f
+#define EXT_RR_START 3u
+
+struct DevCounters {  // mirrors MpCounters (launches is host-side)
+    unsigned long long rays, camera_rays, shadow_rays, inner_visits, packet_visits, leaf_visits;
+};
+
+struct ThreadCounts {
+    uint32_t rays, camera_rays, shadow_rays;
+    Visits vis;
+};
+
+__device__ __forceinline__ void flush_counts(DevCounters* dc, const ThreadCounts& c, bool count_visits) {
+    // every thread of the warp reaches this point (inactive threads carry zeros)
+    uint32_t rays = __reduce_add_sync(0xffffffffu, c.rays);
+    uint32_t cam = __reduce_add_sync(0xffffffffu, c.camera_rays);
+    uint32_t sh = __reduce_add_sync(0xffffffffu, c.shadow_rays);
+    uint32_t vi = 0, vp = 0, vl = 0;
+    if (count_visits) {
+        vi = __reduce_add_sync(0xffffffffu, c.vis.inner);
+        vp = __reduce_add_sync(0xffffffffu, c.vis.packets);
+        vl = __reduce_add_sync(0xffffffffu, c.vis.leaves);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (rays) atomicAdd(&dc->rays, (unsigned long long)rays);
+        if (cam) atomicAdd(&dc->camera_rays, (unsigned long long)cam);
+        if (sh) atomicAdd(&dc->shadow_rays, (unsigned long long)sh);
+        if (count_visits) {
+            atomicAdd(&dc->inner_visits, (unsigned long long)vi);
+            atomicAdd(&dc->packet_visits, (unsigned long long)vp);
+            atomicAdd(&dc->leaf_visits, (unsigned long long)vl);
+        }
+    }
+}
+
+struct TileMap {  // how threads cover tiles: 8x4-pixel micro-tiles, one per warp
+    const MpTile* tiles;
+    uint32_t n_tiles;
+    uint32_t mt_x;              // micro-tiles per tile row = ceil(tile_size / 8)
+    uint32_t threads_per_tile;  // mt_x * ceil(tile_size / 4) * 32
+};
+
+__device__ __forceinline__ bool map_pixel(const TileMap& tm, unsigned long long gid, uint32_t& x, uint32_t& y, uint32_t& tile_index) {
+    const uint32_t ti = (uint32_t)(gid / tm.threads_per_tile);
+    if (ti >= tm.n_tiles) return false;
+    const uint32_t rem = (uint32_t)(gid % tm.threads_per_tile);
+    const uint32_t mt = rem >> 5, l = rem & 31u;
+    const MpTile t = tm.tiles[ti];
+    x = t.min_x + (mt % tm.mt_x) * 8u + (l & 7u);
+    y = t.min_y + (mt / tm.mt_x) * 4u + (l >> 3);
+    tile_index = ti;
+    return x < t.max_x && y < t.max_y;
+}
+
+// Worker::render_sample (worker.rs:51-65) for max_bounces == 0; extension integrator otherwise.
+template <int ORDER, bool COUNT>
+__device__ __forceinline__ float4 render_sample(const Scene& sc, const Camera& cam, uint32_t px, uint32_t py, uint32_t pixel_index,
+                                                uint32_t sample, uint32_t seed_hash, uint32_t max_bounces, ThreadCounts& tc) {
+    uint32_t rng = rng_init(pixel_index, sample, seed_hash);
+    Ray ray = sample_ray(cam, px, py, rng);
+    tc.camera_rays++;
+    if (max_bounces == 0) {
+        tc.rays++;
+        const Hit h = trace<ORDER, COUNT>(sc, ray, false, tc.vis);
+        if (h.tri == MP_NO_HIT) return make_float4(0.f, 0.f, 0.f, 0.f);
+        const F3 n = shading_normal(sc, h);
+        const float d = fabsf(dotn(ray.d, n));
+        return make_float4(d, d, d, 1.0f);
+    }
+    float T = 1.0f, L = 0.0f, alpha = 0.0f;
+    for (uint32_t depth = 0;; ++depth) {
+        tc.rays++;
+        const Hit h = trace<ORDER, COUNT>(sc, ray, false, tc.vis);
+        if (h.tri == MP_NO_HIT) {
+            L = __fadd_rn(L, __fmul_rn(T, EXT_ENV));
+            break;
+        }
+        if (depth == 0) alpha = 1.0f;
+        if (depth == max_bounces) break;
+        F3 n = shading_normal(sc, h);
+        if (dotn(ray.d, n) > 0.0f) n = neg(n);
+        const F3 origin = (ray.o + ray.d * h.t) + n * sc.eps;
+        T = __fmul_rn(T, EXT_ALBEDO);
+        const F3 sun = f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z);
+        const float c = dotn(n, sun);
+        if (c > 0.0f) {
+            const Ray sray = ray_new(origin, sun);
+            tc.rays++, tc.shadow_rays++;
+            const Hit sh = trace<ORDER, COUNT>(sc, sray, true, tc.vis);
+            if (sh.tri == MP_NO_HIT) L = __fadd_rn(L, __fmul_rn(__fmul_rn(T, EXT_SUN_E), c));
+        }
+        if (depth >= EXT_RR_START) {
+            const float q = u01(rng);
+            if (q >= T) break;
+            T = __fdiv_rn(T, T);
+        }
+        float x, y;
+        unit_disc(rng, x, y);
+        const float z = __fsqrt_rn(fmaxf(0.0f, __fsub_rn(1.0f, __fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)))));
+        const float sign = copysignf(1.0f, n.z);
+        const float a = __fdiv_rn(-1.0f, __fadd_rn(sign, n.z));
+        const float b = __fmul_rn(__fmul_rn(n.x, n.y), a);
+        const F3 t1 = f3(__fadd_rn(1.0f, __fmul_rn(__fmul_rn(sign, __fmul_rn(n.x, n.x)), a)), __fmul_rn(sign, b), __fmul_rn(-sign, n.x));
+        const F3 t2 = f3(b, __fadd_rn(sign, __fmul_rn(__fmul_rn(n.y, n.y), a)), -n.y);
+        const F3 dir = (t1 * x + t2 * y) + n * z;
+        ray = ray_new(origin, dir);
+    }
+    return make_float4(L, L, L, alpha);
+}
+
+// Worker::render_tile for many tiles (worker.rs:32-49): one thread per pixel, samples summed sequentially.
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) render_mega_kernel(Scene sc, Camera cam, TileMap tm, float4* __restrict__ film, uint32_t width,
+                                                          uint32_t sample_base, uint32_t sample_count, uint32_t max_bounces,
+                                                          uint32_t seed_hash, DevCounters* dc) {
+    const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x = 0, y = 0, ti = 0;
+    const bool active = map_pixel(tm, gid, x, y, ti);
+    ThreadCounts tc{};
+    if (active) {
+        const uint32_t pixel_index = y * width + x;
+        float4 sum = film[pixel_index];
+        for (uint32_t s = 0; s < sample_count; ++s) {
+            const float4 c = render_sample<ORDER, COUNT>(sc, cam, x, y, pixel_index, sample_base + s, seed_hash, max_bounces, tc);
+            sum.x = __fadd_rn(sum.x, c.x), sum.y = __fadd_rn(sum.y, c.y), sum.z = __fadd_rn(sum.z, c.z), sum.w = __fadd_rn(sum.w, c.w);
+        }
+        film[pixel_index] = sum;
+    }
+    flush_counts(dc, tc, COUNT);
+}
+
+// Object::intersect on caller-provided rays (the bit-exactness gate).  Rays are 36-byte AoS records.
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) trace_rays_kernel(Scene sc, const float* __restrict__ rays, unsigned long long n,
+                                                         uint4* __restrict__ hits, DevCounters* dc) {
+    const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    ThreadCounts tc{};
+    if (i < n) {
+        const float* p = rays + 9 * i;
+        Ray r;
+        r.o = f3(__ldg(p + 0), __ldg(p + 1), __ldg(p + 2));
+        r.d = f3(__ldg(p + 3), __ldg(p + 4), __ldg(p + 5));
+        r.inv = f3(__ldg(p + 6), __ldg(p + 7), __ldg(p + 8));
+        tc.rays = 1;
+        const Hit h = trace<ORDER, COUNT>(sc, r, false, tc.vis);
+        hits[i] = make_uint4(h.tri, __float_as_uint(h.t), __float_as_uint(h.u), __float_as_uint(h.v));
+    }
+    flush_counts(dc, tc, COUNT);
+}
+
+// CameraSampler::sample_ray for every (pixel, sample) of the tiles, written in tile → row-major pixel → sample order.
+__global__ void __launch_bounds__(128) generate_rays_kernel(Camera cam, TileMap tm, const unsigned long long* __restrict__ tile_offsets,
+                                                            uint32_t width, uint32_t sample_base, uint32_t sample_count, uint32_t seed_hash,
+                                                            float* __restrict__ out) {
+    const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x, y, ti;
+    if (!map_pixel(tm, gid, x, y, ti)) return;
+    const MpTile t = tm.tiles[ti];
+    const unsigned long long local = (unsigned long long)(y - t.min_y) * (t.max_x - t.min_x) + (x - t.min_x);
+    for (uint32_t s = 0; s < sample_count; ++s) {
+        uint32_t rng = rng_init(y * width + x, sample_base + s, seed_hash);
+        const Ray r = sample_ray(cam, x, y, rng);
+        float* p = out + 9 * ((tile_offsets[ti] + local) * sample_count + s);
+        p[0] = r.o.x, p[1] = r.o.y, p[2] = r.o.z, p[3] = r.d.x, p[4] = r.d.y, p[5] = r.d.z, p[6] = r.inv.x, p[7] = r.inv.y, p[8] = r.inv.z;
+    }
+}
+
+// pixel_sum * (1/spp) and color_to_image (worker.rs:44,69-76) for the whole film.
+__global__ void __launch_bounds__(256) resolve_kernel(const float4* __restrict__ film, uint32_t n_pixels, float inv_spp,
+                                                      uint32_t* __restrict__ rgba8) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pixels) return;
+    const float4 c = film[i];
+    rgba8[i] = channel_to_u8(__fmul_rn(c.x, inv_spp)) | channel_to_u8(__fmul_rn(c.y, inv_spp)) << 8 |
+               channel_to_u8(__fmul_rn(c.z, inv_spp)) << 16 | channel_to_u8(__fmul_rn(c.w, inv_spp)) << 24;
+}
+
+// Same for the pixels of a tile batch, into a tile-packed buffer [tile][tile_size][tile_size] (the worker's tile
+// `buffer`, machinery.rs:66-67).
+__global__ void __launch_bounds__(128) resolve_tiles_kernel(TileMap tm, const float4* __restrict__ film, uint32_t width, uint32_t tile_size,
+                                                            float inv_spp, uint32_t* __restrict__ out) {
+    const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x, y, ti;
+    if (!map_pixel(tm, gid, x, y, ti)) return;
+    const MpTile t = tm.tiles[ti];
+    const float4 c = film[y * width + x];
+    out[((size_t)ti * tile_size + (y - t.min_y)) * tile_size + (x - t.min_x)] =
+        channel_to_u8(__fmul_rn(c.x, inv_spp)) | channel_to_u8(__fmul_rn(c.y, inv_spp)) << 8 |
+        channel_to_u8(__fmul_rn(c.z, inv_spp)) << 16 | channel_to_u8(__fmul_rn(c.w, inv_spp)) << 24;
+}
+
+}  // namespace mpd

@@ -1,0 +1,206 @@
+// BVH8 traversal + ray/triangle intersection on the device, one thread per ray, in the reference's exact
+// visiting order (reference src/scene/triangle_bvh/ray_bvh_intersection.rs:26-64,104-162;
+// src/geometry/aabb.rs:257-283; src/geometry/triangle.rs:187-216).
+//
+// Layout read here (all 16-byte aligned, fetched with 128-bit loads through the read-only path):
+//   inner[i]      8 x uint4 : 6 x u16x8 child bounds (min.x,min.y,min.z,max.x,max.y,max.z) + 8 links
+//   inner_box[i]  2 x float4: enclosing box (min, size) node i is dequantised against
+//   packets[p]    9 x uint4 : v0.x,v0.y,v0.z,v1.x,...,v2.z as u16x8
+//   packet_box[p] 2 x float4: enclosing box of the leaf that owns packet p
+// The reference carries each child's box on its stack (32-byte entries); the box of a node only depends on its
+// parent's box and quantised bounds, so it is precomputed on the host with the same fma and the device stack
+// entry shrinks to (link, t1) = 8 bytes.  Bit-neutral.
+#pragma once
+#include "device_math.cuh"
+
+namespace mpd {
+
+#define MPD_STACK_MAX 64
+
+struct Scene {
+    const uint4* __restrict__ inner;
+    const float4* __restrict__ inner_box;
+    const uint4* __restrict__ packets;
+    const float4* __restrict__ packet_box;
+    const uint4* __restrict__ tri_shading;
+    const float4* __restrict__ vertices;
+    uint32_t root;
+    float eps;  // extension integrator: origin offset, 1e-4 * scene diagonal
+};
+
+struct Hit {  // LeafHitRecord (ray_bvh_intersection.rs:165-171); the geometric normal is recomputed at finalise
+    float t, u, v;
+    uint32_t tri;
+};
+
+struct Visits {
+    uint32_t inner, packets, leaves;
+};
+
+// One child lane of InnerNode::intersect: dequantise, slab test clamped to [0, max_t].
+// NANPATH is taken only when some inv_direction component is +inf (a zero direction component): only then can
+// (b - o) * inv be 0 * inf = NaN, which aabb.rs:262-267 replaces by -inf / +inf.  Without NaNs, vminps/vmaxps equal
+// fminf/fmaxf up to the sign of a zero, which no comparison below can observe.
+template <bool NANPATH>
+__device__ __forceinline__ bool child_slab(const uint4 (&q)[6], int lane, const F3& bmin, const F3& bsize, const Ray& r,
+                                           float max_t, float& t1_out) {
+    float lox = __fmul_rn(__fsub_rn(dequant(q[0], lane, bsize.x, bmin.x), r.o.x), r.inv.x);
+    float loy = __fmul_rn(__fsub_rn(dequant(q[1], lane, bsize.y, bmin.y), r.o.y), r.inv.y);
+    float loz = __fmul_rn(__fsub_rn(dequant(q[2], lane, bsize.z, bmin.z), r.o.z), r.inv.z);
+    float hix = __fmul_rn(__fsub_rn(dequant(q[3], lane, bsize.x, bmin.x), r.o.x), r.inv.x);
+    float hiy = __fmul_rn(__fsub_rn(dequant(q[4], lane, bsize.y, bmin.y), r.o.y), r.inv.y);
+    float hiz = __fmul_rn(__fsub_rn(dequant(q[5], lane, bsize.z, bmin.z), r.o.z), r.inv.z);
+    float t1, t2;
+    if (NANPATH) {
+        if (lox != lox) lox = MPD_NINF;
+        if (loy != loy) loy = MPD_NINF;
+        if (loz != loz) loz = MPD_NINF;
+        if (hix != hix) hix = MPD_INF;
+        if (hiy != hiy) hiy = MPD_INF;
+        if (hiz != hiz) hiz = MPD_INF;
+        float cminx = minps(lox, hix), cminy = minps(loy, hiy), cminz = minps(loz, hiz);
+        float cmaxx = maxps(lox, hix), cmaxy = maxps(loy, hiy), cmaxz = maxps(loz, hiz);
+        t1 = maxps(maxps(cminx, 0.0f), maxps(cminy, cminz));
+        t2 = minps(minps(cmaxx, max_t), minps(cmaxy, cmaxz));
+    } else {
+        float cminx = fminf(lox, hix), cminy = fminf(loy, hiy), cminz = fminf(loz, hiz);
+        float cmaxx = fmaxf(lox, hix), cmaxy = fmaxf(loy, hiy), cmaxz = fmaxf(loz, hiz);
+        t1 = fmaxf(fmaxf(cminx, 0.0f), fmaxf(cminy, cminz));
+        t2 = fminf(fminf(cmaxx, max_t), fminf(cmaxy, cmaxz));
+    }
+    t1_out = t1;
+    return t1 <= t2;
+}
+
+// One lane of Triangle<WorldPoint8>::intersect + the t-range mask of intersect_triangles
+// (triangle.rs:187-216; ray_bvh_intersection.rs:125).
+__device__ __forceinline__ bool tri_lane(const uint4 (&q)[9], int lane, const F3& bmin, const F3& bsize, const Ray& r,
+                                         float max_t, float& t_out, float& u_out, float& v_out) {
+    F3 v0 = f3(dequant(q[0], lane, bsize.x, bmin.x), dequant(q[1], lane, bsize.y, bmin.y), dequant(q[2], lane, bsize.z, bmin.z));
+    F3 v1 = f3(dequant(q[3], lane, bsize.x, bmin.x), dequant(q[4], lane, bsize.y, bmin.y), dequant(q[5], lane, bsize.z, bmin.z));
+    F3 v2 = f3(dequant(q[6], lane, bsize.x, bmin.x), dequant(q[7], lane, bsize.y, bmin.y), dequant(q[8], lane, bsize.z, bmin.z));
+    F3 e1 = v1 - v0, e2 = v2 - v0;
+    F3 p = fma_cross(r.d, e2);
+    float det = fma_dot(e1, p);
+    float inv = __fdiv_rn(1.0f, det);  // may be infinite; no epsilon test in the reference
+    F3 s = r.o - v0;
+    float u = __fmul_rn(inv, fma_dot(s, p));
+    F3 qv = fma_cross(s, e1);
+    float v = __fmul_rn(inv, fma_dot(r.d, qv));
+    float t = __fmul_rn(inv, fma_dot(e2, qv));
+    t_out = t, u_out = u, v_out = v;
+    return u >= 0.0f && v >= 0.0f && __fadd_rn(u, v) <= 1.0f && t >= 0.0f && t <= max_t;
+}
+
+template <int ORDER, bool COUNT, bool NANPATH>
+__device__ __forceinline__ Hit trace_impl(const Scene& sc, const Ray& r, bool any_hit, Visits& vis) {
+    uint2 stk[MPD_STACK_MAX];  // (link, t1 bits)
+    int sp = 0;
+    stk[sp++] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
+    Hit best{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
+
+    while (sp > 0) {
+        uint2 e = stk[--sp];
+        if (__uint_as_float(e.y) > best.t) continue;  // ray_bvh_intersection.rs:40
+        const uint32_t count = e.x & MP_LINK_COUNT_MASK, index = e.x >> MP_LINK_COUNT_BITS;
+        if (count == 0) {
+            // ---- inner node (ray_bvh_intersection.rs:149-162) ----
+            if (COUNT) vis.inner++;
+            const float4 b0 = __ldg(sc.inner_box + 2 * (size_t)index), b1 = __ldg(sc.inner_box + 2 * (size_t)index + 1);
+            const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
+            const uint4* n = sc.inner + 8 * (size_t)index;
+            uint4 q[6];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) q[k] = __ldg(n + k);
+            const uint4 la = __ldg(n + 6), lb = __ldg(n + 7);
+            const uint32_t links[8] = {la.x, la.y, la.z, la.w, lb.x, lb.y, lb.z, lb.w};
+            const float max_t = best.t;
+            const int base = sp;
+#pragma unroll
+            for (int lane = 0; lane < 8; ++lane) {
+                // NULL children have all-zero bounds and are discarded when popped (:49); skipping them is neutral
+                if (links[lane] == MP_LINK_NULL) continue;
+                float t1;
+                if (child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1)) {
+                    if (ORDER == MP_ORDER_NEAR_FIRST) {
+                        // keep this node's entries sorted far → near (ties: lower lane nearer the top)
+                        int pos = sp;
+                        while (pos > base && __uint_as_float(stk[pos - 1].y) <= t1) {
+                            stk[pos] = stk[pos - 1];
+                            --pos;
+                        }
+                        stk[pos] = make_uint2(links[lane], __float_as_uint(t1));
+                        ++sp;
+                    } else {
+                        stk[sp++] = make_uint2(links[lane], __float_as_uint(t1));  // lane order: lane 7 pops first
+                    }
+                }
+            }
+        } else {
+            // ---- leaf: ≤7 packets of 8 triangles (ray_bvh_intersection.rs:104-141) ----
+            if (COUNT) vis.leaves++, vis.packets += count;
+            const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)index), b1 = __ldg(sc.packet_box + 2 * (size_t)index + 1);
+            const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
+            const float max_t = best.t;  // not updated inside the leaf
+            Hit local{MPD_INF, 0.0f, 0.0f, MP_NO_HIT};
+            for (uint32_t j = 0; j < count; ++j) {
+                const uint4* pk = sc.packets + 9 * (size_t)(index + j);
+                uint4 q[9];
+#pragma unroll
+                for (int k = 0; k < 9; ++k) q[k] = __ldg(pk + k);
+#pragma unroll
+                for (int lane = 0; lane < 8; ++lane) {
+                    float t, u, v;
+                    if (tri_lane(q, lane, bmin, bsize, r, max_t, t, u, v) && t < local.t) {
+                        local.t = t, local.u = u, local.v = v;
+                        local.tri = (index + j) * 8u + (uint32_t)lane;
+                    }
+                }
+            }
+            if (local.t < best.t) {  // :59
+                best = local;
+                if (any_hit) break;
+            }
+        }
+    }
+    return best;
+}
+
+template <int ORDER, bool COUNT>
+__device__ __forceinline__ Hit trace(const Scene& sc, const Ray& r, bool any_hit, Visits& vis) {
+    // |inv| is infinite for a zero (or denormal) direction component
+    const bool nanpath = (fabsf(r.inv.x) == MPD_INF) | (fabsf(r.inv.y) == MPD_INF) | (fabsf(r.inv.z) == MPD_INF);
+    if (nanpath) return trace_impl<ORDER, COUNT, true>(sc, r, any_hit, vis);
+    return trace_impl<ORDER, COUNT, false>(sc, r, any_hit, vis);
+}
+
+// Hit finalisation (ray_bvh_intersection.rs:66-95): shading normal, normalised.
+__device__ __forceinline__ F3 shading_normal(const Scene& sc, const Hit& h) {
+    const uint4 sh = __ldg(sc.tri_shading + h.tri);
+    F3 n;
+    if (sh.w & MP_TRI_FLAT) {
+        // geometric normal = e1 × e2 of the dequantised triangle, unfused (triangle.rs:141-144)
+        const uint32_t p = h.tri >> 3;
+        const int lane = (int)(h.tri & 7u);
+        const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)p), b1 = __ldg(sc.packet_box + 2 * (size_t)p + 1);
+        const uint16_t* q = reinterpret_cast<const uint16_t*>(sc.packets + 9 * (size_t)p);
+        float c[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            const int a = k % 3;
+            const float size = a == 0 ? b1.x : (a == 1 ? b1.y : b1.z), mn = a == 0 ? b0.x : (a == 1 ? b0.y : b0.z);
+            const float rel = __fmul_rn((float)(int)q[k * 8 + lane], MPD_K_INV_U16);
+            c[k] = __fmaf_rn(size, rel, mn);
+        }
+        F3 v0 = f3(c[0], c[1], c[2]), v1 = f3(c[3], c[4], c[5]), v2 = f3(c[6], c[7], c[8]);
+        n = crossn(v1 - v0, v2 - v0);
+    } else {
+        const float w = __fsub_rn(__fsub_rn(1.0f, h.u), h.v);  // triangle.rs:234
+        const float4 n0 = __ldg(sc.vertices + 2 * (size_t)sh.x), n1 = __ldg(sc.vertices + 2 * (size_t)sh.y),
+                     n2 = __ldg(sc.vertices + 2 * (size_t)sh.z);
+        n = (f3(n0.x, n0.y, n0.z) * w + f3(n1.x, n1.y, n1.z) * h.u) + f3(n2.x, n2.y, n2.z) * h.v;
+    }
+    return normalize(n);
+}
+
+}  // namespace mpd

@@ -1,0 +1,244 @@
+// Wavefront pipeline: ray-gen → [trace → shade (+ light sampling → shadow trace) → compact]* → film accumulate.
+// The reference integrates one sample at a time inside Worker::render_tile (src/renderer/worker.rs:32-65); here one
+// pass carries one sample of every pixel of the tile batch through the stages as separate kernels, with path state
+// in HBM (SoA, 16-byte records) and queues of path slots compacted between bounces by warp ballot + block prefix sum.
+// Per-path arithmetic and its order are exactly those of the megakernel (kernels.cuh), so both produce the same film.
+#pragma once
+#include "kernels.cuh"
+
+namespace mpd {
+
+#define WF_MAX_DEPTH 64
+
+struct WavefrontBuffers {
+    size_t cap = 0;               // path slots
+    float4* ray_o = nullptr;      // origin.xyz, throughput T
+    float4* ray_d = nullptr;      // unit direction.xyz, radiance L
+    uint4* hit = nullptr;         // tri, t, u, v
+    uint4* meta = nullptr;        // pixel_index, rng state, depth | alpha << 31, unused
+    uint32_t* queue[2] = {nullptr, nullptr};
+    float4* sh_o = nullptr;       // shadow ray origin.xyz, contribution
+    uint32_t* sh_path = nullptr;
+    uint32_t* counts = nullptr;   // [0 .. WF_MAX_DEPTH+1] queue sizes per depth, then [.. 2*(WF_MAX_DEPTH+1)] shadow queue sizes
+};
+
+inline void wavefront_free(WavefrontBuffers& w) {
+    cudaFree(w.ray_o), cudaFree(w.ray_d), cudaFree(w.hit), cudaFree(w.meta);
+    cudaFree(w.queue[0]), cudaFree(w.queue[1]), cudaFree(w.sh_o), cudaFree(w.sh_path), cudaFree(w.counts);
+    w = WavefrontBuffers{};
+}
+
+inline cudaError_t wavefront_reserve(WavefrontBuffers& w, size_t cap) {
+    if (cap <= w.cap) return cudaSuccess;
+    wavefront_free(w);
+    cudaError_t e;
+#define WF_ALLOC(ptr, bytes) \
+    if ((e = cudaMalloc(&(ptr), (bytes))) != cudaSuccess) return e;
+    WF_ALLOC(w.ray_o, cap * sizeof(float4))
+    WF_ALLOC(w.ray_d, cap * sizeof(float4))
+    WF_ALLOC(w.hit, cap * sizeof(uint4))
+    WF_ALLOC(w.meta, cap * sizeof(uint4))
+    WF_ALLOC(w.queue[0], cap * sizeof(uint32_t))
+    WF_ALLOC(w.queue[1], cap * sizeof(uint32_t))
+    WF_ALLOC(w.sh_o, cap * sizeof(float4))
+    WF_ALLOC(w.sh_path, cap * sizeof(uint32_t))
+    WF_ALLOC(w.counts, 2 * (WF_MAX_DEPTH + 2) * sizeof(uint32_t))
+#undef WF_ALLOC
+    w.cap = cap;
+    return cudaSuccess;
+}
+
+// Stream compaction: every thread of the block calls this; threads with pred get consecutive slots of the queue.
+// Warp ballot gives the intra-warp rank, a prefix sum over the warp totals in shared memory gives the intra-block
+// offset, and one atomicAdd per block reserves the range.
+__device__ __forceinline__ uint32_t block_compact_slot(bool pred, uint32_t* counter) {
+    __shared__ uint32_t warp_base[4];
+    __shared__ uint32_t block_base;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t ballot = __ballot_sync(0xffffffffu, pred);
+    if (lane == 0) warp_base[warp] = __popc(ballot);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const uint32_t c = warp_base[w];
+            warp_base[w] = total;
+            total += c;
+        }
+        block_base = total ? atomicAdd(counter, total) : 0u;
+    }
+    __syncthreads();
+    const uint32_t slot = block_base + warp_base[warp] + __popc(ballot & ((1u << lane) - 1u));
+    __syncthreads();  // shared scratch is reused by the next call
+    return slot;
+}
+
+// Stage 1: CameraSampler::sample_ray (camera.rs:176-191) for sample `sample` of every pixel of the tile batch.
+__global__ void __launch_bounds__(128) wf_raygen_kernel(Camera cam, TileMap tm, uint32_t width, uint32_t sample, uint32_t seed_hash,
+                                                        float4* __restrict__ ray_o, float4* __restrict__ ray_d, uint4* __restrict__ meta,
+                                                        uint32_t* __restrict__ queue, uint32_t* count, DevCounters* dc) {
+    const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x = 0, y = 0, ti = 0;
+    const bool active = map_pixel(tm, gid, x, y, ti);
+    ThreadCounts tc{};
+    if (active) {
+        const uint32_t pixel_index = y * width + x;
+        uint32_t rng = rng_init(pixel_index, sample, seed_hash);
+        const Ray r = sample_ray(cam, x, y, rng);
+        ray_o[gid] = make_float4(r.o.x, r.o.y, r.o.z, 1.0f);
+        ray_d[gid] = make_float4(r.d.x, r.d.y, r.d.z, 0.0f);
+        meta[gid] = make_uint4(pixel_index, rng, 0u, 0u);
+        tc.camera_rays = 1;
+    }
+    const uint32_t slot = block_compact_slot(active, count);
+    if (active) queue[slot] = (uint32_t)gid;
+    flush_counts(dc, tc, false);
+}
+
+__device__ __forceinline__ Ray load_ray(const float4 o, const float4 d) {
+    Ray r;
+    r.o = f3(o.x, o.y, o.z);
+    r.d = f3(d.x, d.y, d.z);
+    // same expression as Ray::new on the same unit direction (geometry/mod.rs:47)
+    r.inv.x = r.d.x == 0.0f ? MPD_INF : __fdiv_rn(1.0f, r.d.x);
+    r.inv.y = r.d.y == 0.0f ? MPD_INF : __fdiv_rn(1.0f, r.d.y);
+    r.inv.z = r.d.z == 0.0f ? MPD_INF : __fdiv_rn(1.0f, r.d.z);
+    return r;
+}
+
+// Stage 2: closest-hit traversal of the queued paths.
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) wf_trace_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
+                                                       const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
+                                                       uint4* __restrict__ hit, DevCounters* dc) {
+    const uint32_t n = *count;
+    if (blockIdx.x * blockDim.x >= n) return;  // whole block idle
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    ThreadCounts tc{};
+    if (i < n) {
+        const uint32_t path = queue[i];
+        const Ray r = load_ray(ray_o[path], ray_d[path]);
+        tc.rays = 1;
+        const Hit h = trace<ORDER, COUNT>(sc, r, false, tc.vis);
+        hit[path] = make_uint4(h.tri, __float_as_uint(h.t), __float_as_uint(h.u), __float_as_uint(h.v));
+    }
+    flush_counts(dc, tc, COUNT);
+}
+
+// Stage 3: hit finalisation + shading + light/BSDF sampling; survivors are compacted into the next queue and
+// shadow rays into the shadow queue.
+__global__ void __launch_bounds__(128) wf_shade_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
+                                                       uint32_t* __restrict__ next_queue, uint32_t* next_count,
+                                                       float4* __restrict__ sh_o, uint32_t* __restrict__ sh_path, uint32_t* sh_count,
+                                                       float4* __restrict__ ray_o, float4* __restrict__ ray_d, const uint4* __restrict__ hit,
+                                                       uint4* __restrict__ meta, uint32_t max_bounces) {
+    const uint32_t n = *count;
+    if (blockIdx.x * blockDim.x >= n) return;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool survive = false, shadow = false;
+    uint32_t path = 0;
+    float4 so = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < n) {
+        path = queue[i];
+        const float4 o4 = ray_o[path];
+        float4 d4 = ray_d[path];
+        const uint4 h4 = hit[path];
+        uint4 m = meta[path];
+        const Hit h{__uint_as_float(h4.y), __uint_as_float(h4.z), __uint_as_float(h4.w), h4.x};
+        const F3 ro = f3(o4.x, o4.y, o4.z), rd = f3(d4.x, d4.y, d4.z);
+        float T = o4.w, L = d4.w;
+        const uint32_t depth = m.z & 0x7fffffffu;
+        if (max_bounces == 0) {  // the reference shader (worker.rs:57-64)
+            if (h.tri != MP_NO_HIT) {
+                L = fabsf(dotn(rd, shading_normal(sc, h)));
+                m.z |= 0x80000000u;
+            }
+            ray_d[path].w = L;
+            meta[path].z = m.z;
+        } else if (h.tri == MP_NO_HIT) {
+            ray_d[path].w = __fadd_rn(L, __fmul_rn(T, EXT_ENV));
+        } else {
+            if (depth == 0) m.z |= 0x80000000u;
+            if (depth != max_bounces) {
+                F3 nrm = shading_normal(sc, h);
+                if (dotn(rd, nrm) > 0.0f) nrm = neg(nrm);
+                const F3 origin = (ro + rd * h.t) + nrm * sc.eps;
+                T = __fmul_rn(T, EXT_ALBEDO);
+                const float c = dotn(nrm, f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
+                if (c > 0.0f) {
+                    shadow = true;
+                    so = make_float4(origin.x, origin.y, origin.z, __fmul_rn(__fmul_rn(T, EXT_SUN_E), c));
+                }
+                survive = true;
+                if (depth >= EXT_RR_START) {
+                    const float q = u01(m.y);
+                    if (q >= T)
+                        survive = false;
+                    else
+                        T = __fdiv_rn(T, T);
+                }
+                if (survive) {
+                    float x, y;
+                    unit_disc(m.y, x, y);
+                    const float z = __fsqrt_rn(fmaxf(0.0f, __fsub_rn(1.0f, __fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)))));
+                    const float sign = copysignf(1.0f, nrm.z);
+                    const float a = __fdiv_rn(-1.0f, __fadd_rn(sign, nrm.z));
+                    const float b = __fmul_rn(__fmul_rn(nrm.x, nrm.y), a);
+                    const F3 t1 = f3(__fadd_rn(1.0f, __fmul_rn(__fmul_rn(sign, __fmul_rn(nrm.x, nrm.x)), a)), __fmul_rn(sign, b), __fmul_rn(-sign, nrm.x));
+                    const F3 t2 = f3(b, __fadd_rn(sign, __fmul_rn(__fmul_rn(nrm.y, nrm.y), a)), -nrm.y);
+                    const F3 dir = (t1 * x + t2 * y) + nrm * z;
+                    const Ray nr = ray_new(origin, dir);
+                    ray_o[path] = make_float4(nr.o.x, nr.o.y, nr.o.z, T);
+                    ray_d[path] = make_float4(nr.d.x, nr.d.y, nr.d.z, L);
+                    m.z = (m.z & 0x80000000u) | (depth + 1u);
+                }
+            }
+            meta[path] = m;
+        }
+    }
+    const uint32_t sslot = block_compact_slot(shadow, sh_count);
+    if (shadow) {
+        sh_o[sslot] = so;
+        sh_path[sslot] = path;
+    }
+    const uint32_t slot = block_compact_slot(survive, next_count);
+    if (survive) next_queue[slot] = path;
+}
+
+// Stage 3b: any-hit traversal of the light-sampling rays; unoccluded ones add their contribution to the path.
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) wf_shadow_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
+                                                        const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, DevCounters* dc) {
+    const uint32_t n = *sh_count;
+    if (blockIdx.x * blockDim.x >= n) return;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    ThreadCounts tc{};
+    if (i < n) {
+        const float4 o = sh_o[i];
+        const Ray r = ray_new(f3(o.x, o.y, o.z), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
+        tc.rays = 1, tc.shadow_rays = 1;
+        const Hit h = trace<ORDER, COUNT>(sc, r, true, tc.vis);
+        if (h.tri == MP_NO_HIT) {
+            const uint32_t path = sh_path[i];
+            ray_d[path].w = __fadd_rn(ray_d[path].w, o.w);
+        }
+    }
+    flush_counts(dc, tc, COUNT);
+}
+
+// Stage 4: film accumulation (worker.rs:42): film[pixel] += (L, L, L, alpha) for the pass's sample.
+__global__ void __launch_bounds__(128) wf_accumulate_kernel(TileMap tm, float4* __restrict__ film, const float4* __restrict__ ray_d,
+                                                            const uint4* __restrict__ meta) {
+    const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x, y, ti;
+    if (!map_pixel(tm, gid, x, y, ti)) return;
+    const uint4 m = meta[gid];
+    const float L = ray_d[gid].w;
+    const float alpha = (m.z & 0x80000000u) ? 1.0f : 0.0f;
+    float4 f = film[m.x];
+    f.x = __fadd_rn(f.x, L), f.y = __fadd_rn(f.y, L), f.z = __fadd_rn(f.z, L), f.w = __fadd_rn(f.w, alpha);
+    film[m.x] = f;
+}
+
+}  // namespace mpd
