@@ -1,0 +1,63 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+DATA = os.path.join(ROOT, "data")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from oracle_lib import Oracle
+
+    return Oracle()
+
+
+@pytest.fixture(scope="session")
+def teapot():
+    import minipath_b200 as mp
+
+    return mp.TriangleBvh.with_obj(os.path.join(DATA, "teapot.obj"))
+
+
+@pytest.fixture(scope="session")
+def cube():
+    import minipath_b200 as mp
+
+    return mp.TriangleBvh.with_obj(os.path.join(DATA, "cube.obj"), quad_mode=1)
+
+
+@pytest.fixture(scope="session")
+def teapot_camera():
+    """The camera of benches/render_teapot.rs:12-19 and src/cli.rs:13-20."""
+    import minipath_b200 as mp
+
+    return mp.Camera.default().look_at((0.0, 2.0, 10.0), (0.0, 1.5, 0.0), (0.0, 1.0, 0.0)).f_number(4.8).focus_distance(10.0)
+
+
+@pytest.fixture(scope="session")
+def cube_camera():
+    """SURVEY §8(d) gate camera for the fan-triangulated cube: pinhole-ish f/64."""
+    import minipath_b200 as mp
+
+    return mp.Camera.default().look_at((1.5, 1.2, 2.5), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0)).f_number(64.0)
+
+
+@pytest.fixture(scope="session")
+def gpu_ctx():
+    import minipath_b200 as mp
+
+    if mp.device_count() == 0:
+        pytest.fail("no CUDA device: -m gpu tests need a B200 (there is no CPU fallback)")
+    ctx = mp.Context(0)
+    yield ctx
+    ctx.close()

@@ -1,0 +1,194 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bar: bit-exact.  Hit records are compared as raw bit patterns; films as raw f32 bits; images as u8.
+"""
+import numpy as np
+import pytest
+
+import minipath_b200 as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint8)
+
+
+def _assert_hits_equal(h_gpu, h_cpu):
+    bad = np.nonzero(_bits(h_gpu).reshape(len(h_gpu), -1) != _bits(h_cpu).reshape(len(h_cpu), -1))[0]
+    assert len(bad) == 0, f"{len(np.unique(bad))} of {len(h_gpu)} rays differ, first: gpu={h_gpu[bad[0]]} cpu={h_cpu[bad[0]]}"
+
+
+def _setup(ctx, bvh, camera, w, h):
+    ctx.upload_scene(bvh)
+    s = camera.build_sampler((w, h))
+    ctx.set_camera(s)
+    ctx.create_film(w, h)
+    return s
+
+
+@pytest.mark.parametrize("scene_name", ["teapot", "cube"])
+def test_raygen_bit_exact(gpu_ctx, oracle, request, scene_name):
+    """CameraSampler::sample_ray (camera.rs:176-191) incl. Ray::new: device rays == oracle rays, bit for bit."""
+    bvh = request.getfixturevalue(scene_name)
+    cam = request.getfixturevalue(scene_name + "_camera")
+    w, h = 200, 120  # ragged: 200 = 3*64+8, 120 = 64+56
+    s = _setup(gpu_ctx, bvh, cam, w, h)
+    st = mp.RenderSettings(64, 3, (w, h), seed=0xC0FFEE)
+    tiles = mp.full_screen_tiles(w, h, 64, seed=5)
+    r_gpu = gpu_ctx.generate_rays(tiles, st.params())
+    r_cpu = oracle.generate_rays(s, w, tiles, st.params())
+    assert r_gpu.shape == r_cpu.shape == (w * h * 3,)
+    assert np.array_equal(_bits(r_gpu), _bits(r_cpu))
+
+
+@pytest.mark.parametrize("scene_name", ["teapot", "cube"])
+@pytest.mark.parametrize("order", [mp.ORDER_REFERENCE, mp.ORDER_NEAR_FIRST])
+def test_primary_hits_bit_exact(gpu_ctx, oracle, request, scene_name, order):
+    """The gate of BASELINE.json configs[1]: triangle index and t (and u, v) of primary rays, bit-exact."""
+    bvh = request.getfixturevalue(scene_name)
+    cam = request.getfixturevalue(scene_name + "_camera")
+    w, h = 320, 180
+    s = _setup(gpu_ctx, bvh, cam, w, h)
+    st = mp.RenderSettings(64, 4, (w, h), seed=1234)
+    tiles = mp.full_screen_tiles(w, h, 64, seed=9)
+    rays = oracle.generate_rays(s, w, tiles, st.params())
+    h_gpu = gpu_ctx.trace_rays(rays, order)
+    h_cpu = oracle.trace_rays(bvh, rays, order)
+    assert (h_cpu["tri"] != mp.NO_HIT).sum() > 1000
+    _assert_hits_equal(h_gpu, h_cpu)
+
+
+def test_incoherent_and_degenerate_rays(gpu_ctx, oracle, teapot, cube):
+    """Random incoherent rays plus the edge cases of aabb.rs:433-471: axis-parallel directions (0*inf → NaN path),
+    origins on box faces, rays starting inside, rays pointing away."""
+    rng = np.random.default_rng(42)
+    for bvh in (teapot, cube):
+        lo, hi = bvh.get_bounding_box()
+        n = 20000
+        o = rng.uniform(lo - 1.0, hi + 1.0, (n, 3)).astype(np.float32)
+        d = rng.normal(size=(n, 3)).astype(np.float32)
+        # axis-parallel and plane-parallel directions
+        d[:3000, 0] = 0.0
+        d[1000:4000, 1] = 0.0
+        d[2000:2500, 2] = 0.0
+        d[2400:2500] = (0.0, 0.0, 1.0)
+        # origins exactly on the bounding box faces and corners
+        o[4000:4500, 0] = lo[0]
+        o[4500:5000, 1] = hi[1]
+        o[5000:5100] = lo
+        o[5100:5200] = hi
+        d[d.sum(axis=1) == 0] = (1.0, 0.0, 0.0)
+        rays = oracle.rays_from(o, d)
+        gpu_ctx.upload_scene(bvh)
+        for order in (mp.ORDER_REFERENCE, mp.ORDER_NEAR_FIRST):
+            _assert_hits_equal(gpu_ctx.trace_rays(rays, order), oracle.trace_rays(bvh, rays, order))
+
+
+@pytest.mark.parametrize("mode", [mp.MODE_MEGAKERNEL, mp.MODE_WAVEFRONT])
+@pytest.mark.parametrize("scene_name", ["teapot", "cube"])
+def test_reference_shader_film_bit_exact(gpu_ctx, oracle, request, scene_name, mode):
+    """Worker::render_tile + color_to_image (worker.rs:32-76), bounce 0: f32 film and RGBA8 image identical."""
+    bvh = request.getfixturevalue(scene_name)
+    cam = request.getfixturevalue(scene_name + "_camera")
+    w, h = 200, 136
+    s = _setup(gpu_ctx, bvh, cam, w, h)
+    st = mp.RenderSettings(64, 5, (w, h), seed=99, mode=mode)
+    tiles = mp.full_screen_tiles(w, h, 64, seed=3)
+    gpu_ctx.render_tiles(tiles, st.params())
+    film_gpu = gpu_ctx.read_film()
+    img_gpu = gpu_ctx.resolve_rgba8(5)
+    film_cpu, _, _ = oracle.render_tiles(bvh, s, w, h, tiles, st.params())
+    assert film_cpu[..., 3].sum() > 0
+    assert np.array_equal(_bits(film_gpu), _bits(film_cpu))
+    assert np.array_equal(img_gpu, oracle.resolve_rgba8(film_cpu, 5))
+
+
+@pytest.mark.parametrize("mode", [mp.MODE_MEGAKERNEL, mp.MODE_WAVEFRONT])
+@pytest.mark.parametrize("bounces", [1, 5])
+def test_extension_integrator_film_bit_exact(gpu_ctx, oracle, teapot, teapot_camera, mode, bounces):
+    """max_bounces > 0 (extension; no reference behaviour): megakernel, wavefront and oracle agree bit for bit,
+    and the ray counters agree."""
+    w, h = 160, 120
+    s = _setup(gpu_ctx, teapot, teapot_camera, w, h)
+    st = mp.RenderSettings(32, 3, (w, h), max_bounces=bounces, seed=2024, mode=mode)
+    tiles = mp.full_screen_tiles(w, h, 32, seed=3)
+    gpu_ctx.reset_counters()
+    gpu_ctx.enable_counters(True)
+    gpu_ctx.render_tiles(tiles, st.params())
+    film_gpu = gpu_ctx.read_film()
+    c_gpu = gpu_ctx.counters()
+    gpu_ctx.enable_counters(False)
+    film_cpu, _, c_cpu = oracle.render_tiles(teapot, s, w, h, tiles, st.params())
+    assert np.array_equal(_bits(film_gpu), _bits(film_cpu))
+    assert c_gpu["rays"] == c_cpu.rays and c_gpu["shadow_rays"] == c_cpu.shadow_rays and c_gpu["camera_rays"] == c_cpu.camera_rays
+    assert c_gpu["inner_visits"] == c_cpu.inner_visits and c_gpu["packet_visits"] == c_cpu.packet_visits
+
+
+def test_progressive_passes_equal_one_pass(gpu_ctx, teapot, teapot_camera):
+    """Samples are summed sequentially per pixel: 2 + 3 samples in two calls == 5 samples in one."""
+    w, h = 128, 96
+    _setup(gpu_ctx, teapot, teapot_camera, w, h)
+    st = mp.RenderSettings(64, 5, (w, h), seed=5)
+    tiles = mp.full_screen_tiles(w, h, 64, seed=3)
+    gpu_ctx.render_tiles(tiles, st.params())
+    one = gpu_ctx.read_film()
+    gpu_ctx.clear_film()
+    gpu_ctx.render_tiles(tiles, st.params(sample_count=2, sample_base=0))
+    gpu_ctx.render_tiles(tiles, st.params(sample_count=3, sample_base=2))
+    assert np.array_equal(_bits(gpu_ctx.read_film()), _bits(one))
+
+
+def test_tile_order_independence(gpu_ctx, teapot, teapot_camera):
+    """Pixels do not depend on the tile order, tile size or batching (RNG is keyed on the pixel, not the tile)."""
+    w, h = 150, 100
+    _setup(gpu_ctx, teapot, teapot_camera, w, h)
+    films = []
+    for ts, seed in ((64, 1), (64, 2), (32, 3), (17, 4)):
+        gpu_ctx.clear_film()
+        st = mp.RenderSettings(ts, 2, (w, h), seed=77)
+        tiles = mp.full_screen_tiles(w, h, ts, seed=seed)
+        half = len(tiles) // 2
+        gpu_ctx.render_tiles(tiles[:half], st.params())
+        gpu_ctx.render_tiles(tiles[half:], st.params())
+        films.append(gpu_ctx.read_film())
+    for f in films[1:]:
+        assert np.array_equal(_bits(f), _bits(films[0]))
+
+
+def test_render_api_matches_oracle(oracle, teapot, teapot_camera):
+    """minipath::render (machinery.rs:20-123): callbacks, progress, and an image identical to the oracle's."""
+    w, h = 256, 192
+    st = mp.RenderSettings(64, 4, (w, h), seed=31337, tiles_per_batch=3)
+    started, finished = [], []
+    prog = mp.render(mp.Scene(teapot), teapot_camera, st, lambda t: started.append(t), lambda t, s: finished.append((t, s.finished, s.total)), devices=[0])
+    prog.wait()
+    assert prog.is_finished()
+    img = prog.image()
+    tiles = mp.full_screen_tiles(w, h, 64)
+    assert len(started) == len(finished) == len(tiles) == 12
+    assert set(started) == {mp.ScreenBlock((t["min_x"], t["min_y"]), (t["max_x"], t["max_y"])) for t in tiles}
+    assert all(total == 12 for _, _, total in finished)
+    assert prog.progress().finished == 12 and prog.elapsed() > 0
+    film_cpu, _, _ = oracle.render_tiles(teapot, teapot_camera.build_sampler((w, h)), w, h, tiles, st.params())
+    assert np.array_equal(img, oracle.resolve_rgba8(film_cpu, 4))
+
+
+def test_full_size_properties(gpu_ctx, teapot, teapot_camera):
+    """BASELINE.json configs[0] at full size (2048x1536, 10 spp) through size-independent properties: alpha is the
+    hit fraction in [0,1], colour <= alpha, the image is left-right plausible, and two runs are identical."""
+    w, h = 2048, 1536
+    _setup(gpu_ctx, teapot, teapot_camera, w, h)
+    st = mp.RenderSettings(64, 10, (w, h), seed=1)
+    tiles = mp.full_screen_tiles(w, h, 64)
+    assert len(tiles) == 768
+    gpu_ctx.render_tiles(tiles, st.params())
+    film = gpu_ctx.read_film()
+    gpu_ctx.clear_film()
+    gpu_ctx.render_tiles(tiles[::-1].copy(), st.params())
+    assert np.array_equal(_bits(film), _bits(gpu_ctx.read_film()))
+    a = film[..., 3]
+    assert a.min() >= 0 and a.max() <= 10 and np.all(a == np.round(a))
+    assert np.all(film[..., 0] <= a + 1e-4) and np.all(film[..., 0] == film[..., 1]) and np.all(film[..., 1] == film[..., 2])
+    assert 0.15 < (a > 0).mean() < 0.6  # the teapot covers a good part of the frame
+    assert a[:50].sum() == 0 and a[-50:].sum() == 0  # top/bottom rows are background
