@@ -212,6 +212,11 @@ int mp_counters_reset(MpCtx* ctx);
 /* Device time (ms, CUDA events on the launching stream) of the last render/trace call's kernels. */
 int mp_last_device_ms(MpCtx* ctx, float* out_ms);
 
+/* Roofline denominators not in MEASURED_PEAKS.json, measured on this device (no reference counterpart):
+ * FP32 FMA throughput (TFLOP/s, 2 flop per FMA) and L2 read bandwidth (GB/s) over a buffer of `bytes`. */
+int mp_probe_fp32_tflops(MpCtx* ctx, float* out_tflops);
+int mp_probe_l2_gbs(MpCtx* ctx, size_t bytes, float* out_gbs);
+
 /* Scene<TriangleBvh> → device (borrowed host arrays are copied; caller keeps ownership). */
 int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* bvh);
 /* CameraSampler for the render (camera.build_sampler(resolution), machinery.rs:65). */
@@ -229,6 +234,8 @@ int mp_film_device_ptr(MpCtx* ctx, void** out);
 int mp_render_tiles(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, const MpRenderParams* params);
 /* pixel_sum * (1/spp) then color_to_image (worker.rs:44,69-76) for the whole film → host RGBA8. Synchronises. */
 int mp_film_resolve_rgba8(MpCtx* ctx, uint32_t spp_total, uint8_t* host_out);
+/* Same, into caller-owned device memory (width*height RGBA8 words); asynchronous on the context's stream. */
+int mp_film_resolve_device(MpCtx* ctx, uint32_t spp_total, void* dev_out);
 /* Same for n tiles only, into a tile-packed host buffer [n_tiles][tile_size][tile_size] RGBA8 — the worker's
  * `buffer` of machinery.rs:66-67 for a whole batch; only the first (w x h) of each tile slot is written. Synchronises. */
 int mp_film_resolve_tiles_rgba8(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, uint32_t tile_size, uint32_t spp_total,

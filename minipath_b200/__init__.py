@@ -415,6 +415,16 @@ class Context:
         check(lib.mp_last_device_ms(self._h, C.byref(ms)))
         return ms.value
 
+    def probe_fp32_tflops(self):
+        out = C.c_float()
+        check(lib.mp_probe_fp32_tflops(self._h, C.byref(out)))
+        return out.value
+
+    def probe_l2_gbs(self, nbytes=32 << 20):
+        out = C.c_float()
+        check(lib.mp_probe_l2_gbs(self._h, nbytes, C.byref(out)))
+        return out.value
+
     def upload_scene(self, bvh):
         check(lib.mp_scene_upload(self._h, bvh._ptr))
 
@@ -441,6 +451,9 @@ class Context:
         img = np.empty((h, w, 4), np.uint8) if out is None else out
         check(lib.mp_film_resolve_rgba8(self._h, spp_total, img.ctypes.data))
         return img
+
+    def resolve_device(self, spp_total, device_ptr):
+        check(lib.mp_film_resolve_device(self._h, spp_total, device_ptr))
 
     def resolve_tiles_rgba8(self, tiles, tile_size, spp_total):
         arr, ptr, n = _tiles_arg(tiles)

@@ -190,6 +190,8 @@ PROTOTYPES = {
     "mp_counters": (_i, [_vp, _P(MpCounters)]),
     "mp_counters_reset": (_i, [_vp]),
     "mp_last_device_ms": (_i, [_vp, _P(C.c_float)]),
+    "mp_probe_fp32_tflops": (_i, [_vp, _P(C.c_float)]),
+    "mp_probe_l2_gbs": (_i, [_vp, C.c_size_t, _P(C.c_float)]),
     "mp_scene_upload": (_i, [_vp, _P(MpFlatBvh)]),
     "mp_camera_set": (_i, [_vp, _P(MpCameraSampler)]),
     "mp_film_create": (_i, [_vp, _u32, _u32]),
@@ -198,6 +200,7 @@ PROTOTYPES = {
     "mp_film_device_ptr": (_i, [_vp, _P(_vp)]),
     "mp_render_tiles": (_i, [_vp, _P(MpTile), _u32, _P(MpRenderParams)]),
     "mp_film_resolve_rgba8": (_i, [_vp, _u32, _vp]),
+    "mp_film_resolve_device": (_i, [_vp, _u32, _vp]),
     "mp_film_resolve_tiles_rgba8": (_i, [_vp, _P(MpTile), _u32, _u32, _u32, _vp]),
     "mp_film_read_f32": (_i, [_vp, _vp]),
     "mp_trace_rays": (_i, [_vp, _vp, _u64, _u32, _vp]),

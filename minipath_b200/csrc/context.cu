@@ -6,6 +6,7 @@
 #include "host_common.h"
 #include "kernels.cuh"
 #include "wavefront.cuh"
+#include "probes.cuh"
 
 using namespace mp;
 
@@ -44,6 +45,7 @@ struct MpCtx {
     // tile staging
     MpTile* d_tiles = nullptr;
     size_t tiles_cap = 0;
+    size_t tiles_staged = 0;
     MpTile* h_tiles_pinned = nullptr;
     // wavefront state
     mpd::WavefrontBuffers wf{};
@@ -73,10 +75,14 @@ static int stage_tiles(MpCtx* ctx, const MpTile* tiles, uint32_t n) {
         CK(cudaMalloc(&ctx->d_tiles, cap * sizeof(MpTile)));
         CK(cudaMallocHost(&ctx->h_tiles_pinned, cap * sizeof(MpTile)));
         ctx->tiles_cap = cap;
+        ctx->tiles_staged = 0;
     } else {
+        // same tile list as the previous call (a frame re-rendered, the next sample pass): already on the device
+        if (n == ctx->tiles_staged && memcmp(ctx->h_tiles_pinned, tiles, n * sizeof(MpTile)) == 0) return MP_OK;
         // the pinned staging buffer may still be in flight from the previous call on this stream
         CK(cudaStreamSynchronize(ctx->stream));
     }
+    ctx->tiles_staged = n;
     memcpy(ctx->h_tiles_pinned, tiles, n * sizeof(MpTile));
     CK(cudaMemcpyAsync(ctx->d_tiles, ctx->h_tiles_pinned, n * sizeof(MpTile), cudaMemcpyHostToDevice, ctx->stream));
     return MP_OK;
@@ -310,3 +316,4 @@ int mp_film_device_ptr(MpCtx* ctx, void** out) {
 }  // extern "C"
 
 #include "context_render.inc"
+#include "context_probes.inc"

@@ -152,7 +152,9 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
         return rc;
     }
     p->worker_count = devs.size();
-    p->batch = settings->tiles_per_batch ? settings->tiles_per_batch : 32;
+    // default batch: a quarter of each device's share, at least 32 tiles — big enough to fill 148 SMs for several waves,
+    // small enough that the dynamic queue still balances the tail and callbacks keep arriving
+    p->batch = settings->tiles_per_batch ? settings->tiles_per_batch : std::max<size_t>(32, n_tiles / (4 * devs.size()));
     p->started = started, p->finished = finished, p->user = user;
     p->start_time = std::chrono::steady_clock::now();
     try {
