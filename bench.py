@@ -47,7 +47,9 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="teapot-1080p", choices=sorted(WORKLOADS))
-    ap.add_argument("--mode", default="auto", choices=["auto", "megakernel", "wavefront"])
+    ap.add_argument("--mode", default="auto", choices=["auto", "megakernel", "wavefront", "wavefront-thread"],
+                    help="megakernel: one thread per pixel; wavefront: staged kernels with the octet traversal kernel; "
+                         "wavefront-thread: staged kernels with the thread-per-ray traversal kernel")
     ap.add_argument("--order", default="reference", choices=["reference", "near_first"])
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel")
     ap.add_argument("--bounces", type=int, default=-1, help="override the workload's max_bounces")
@@ -234,12 +236,17 @@ def run_b200(args, rank, local, world):
     def reduce_fn(t):
         dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
 
-    def make_step(mode):
+    modes = {"megakernel": mp.MODE_MEGAKERNEL, "wavefront": mp.MODE_WAVEFRONT, "wavefront-thread": mp.MODE_WAVEFRONT}
+
+    def make_step(mode_key):
+        mode = modes[mode_key]
+
         def render_fn(sub_tiles, base, count):
             st = mp.RenderSettings(64, count, (w, h), max_bounces=bounces, seed=7, mode=mode, order=order)
             ctx.render_tiles(sub_tiles, st.params(sample_base=base))
 
         def step():
+            ctx.set_trace_variant(mp.TRACE_THREAD if mode_key == "wavefront-thread" else mp.TRACE_OCTET)
             film.zero_()
             # weak scaling: every rank renders the full frame with its own `spp` sample indices; total spp = spp * world
             mpdist.render_sharded(render_fn, film, tiles, spp * world if args.shard == "spp" else spp, rank, world, args.shard,
@@ -271,20 +278,19 @@ def run_b200(args, rank, local, world):
         torch.cuda.synchronize()
 
     # ---- pick the pipeline: the A/B the north_star asks for, measured here, reported in config ----
-    modes = {"megakernel": mp.MODE_MEGAKERNEL, "wavefront": mp.MODE_WAVEFRONT}
     ab = {}
     if args.mode == "auto":
-        for name, m in modes.items():
+        for name in modes:
             barrier()
-            ab[name] = timed(make_step(m), 1, 1)
+            ab[name] = timed(make_step(name), 1, 1)
         if world > 1:
-            t = torch.tensor([ab["megakernel"], ab["wavefront"]], device="cuda")
+            t = torch.tensor([ab[k] for k in modes], device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ab = {"megakernel": float(t[0]), "wavefront": float(t[1])}
+            ab = {k: float(t[i]) for i, k in enumerate(modes)}
         mode_name = min(ab, key=ab.get)
     else:
         mode_name = args.mode
-    step = make_step(modes[mode_name])
+    step = make_step(mode_name)
 
     # ---- counted pass (untimed): rays and node visits of one step, deterministic for a given seed ----
     ctx.enable_counters(True)
@@ -409,7 +415,8 @@ def roofline(args, res):
         out = {"bound": mem_bound[0], "achieved": bytes_ / secs / 1e9, "peak": mem_bound[2], "unit": "GB/s", "frac": mem_bound[1] / secs}
     out.update({
         "traffic": None,
-        "kernel": "render_mega_kernel" if res["mode_name"] == "megakernel" else "wf_trace_kernel+wf_shadow_kernel (share of step: see profiles/)",
+        "kernel": {"megakernel": "render_mega_kernel", "wavefront": "wf_trace_octet_kernel+wf_shadow_octet_kernel",
+                   "wavefront-thread": "wf_trace_kernel+wf_shadow_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
         "peak_source": "FP32 FMA and L2 read bandwidth measured by mp_probe_* in this run; HBM " + hbm_src,
         "fp32": {"achieved_tflops": flops / secs / 1e12, "peak_tflops": fp32, "frac": t_fp32 / secs},
         "l2": {"achieved_gbs": bytes_ / secs / 1e9, "peak_gbs": l2, "frac": t_l2 / secs},

@@ -205,6 +205,12 @@ int mp_ctx_destroy(MpCtx* ctx);
 /* Run on a caller-owned CUDA stream (cudaStream_t as void*); NULL → the context's own stream. */
 int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream);
 int mp_ctx_sync(MpCtx* ctx);
+/* Which traversal kernel serves mp_trace_rays* and the wavefront pipeline (same visiting order, same bits):
+ * THREAD = one thread per ray, SoA node rows, local-memory stack (trace.cuh);
+ * OCTET  = eight lanes per ray, child-major 16-byte records, shared-memory stack, self-refilling octets (octet.cuh; default). */
+#define MP_TRACE_THREAD 0u
+#define MP_TRACE_OCTET 1u
+int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant);
 /* Count traversal work (adds a few atomics per warp); off by default. */
 int mp_ctx_enable_counters(MpCtx* ctx, int on);
 int mp_counters(MpCtx* ctx, MpCounters* out);

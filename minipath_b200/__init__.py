@@ -17,6 +17,8 @@ from ._ffi import (  # noqa: F401  (re-exported)
     NO_HIT,
     ORDER_NEAR_FIRST,
     ORDER_REFERENCE,
+    TRACE_OCTET,
+    TRACE_THREAD,
     MpError,
     check,
     lib,
@@ -395,6 +397,9 @@ class Context:
 
     def set_stream(self, cuda_stream_ptr):
         check(lib.mp_ctx_set_stream(self._h, cuda_stream_ptr))
+
+    def set_trace_variant(self, variant):
+        check(lib.mp_ctx_set_trace_variant(self._h, variant))
 
     def sync(self):
         check(lib.mp_ctx_sync(self._h))

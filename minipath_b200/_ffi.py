@@ -18,6 +18,7 @@ NO_HIT = 0xFFFFFFFF
 TRI_FLAT = 0x80000000
 MODE_MEGAKERNEL, MODE_WAVEFRONT = 0, 1
 ORDER_REFERENCE, ORDER_NEAR_FIRST = 0, 1
+TRACE_THREAD, TRACE_OCTET = 0, 1
 
 
 class MpError(RuntimeError):
@@ -185,6 +186,7 @@ PROTOTYPES = {
     "mp_ctx_create": (_i, [_i, _P(_vp)]),
     "mp_ctx_destroy": (_i, [_vp]),
     "mp_ctx_set_stream": (_i, [_vp, _vp]),
+    "mp_ctx_set_trace_variant": (_i, [_vp, _u32]),
     "mp_ctx_sync": (_i, [_vp]),
     "mp_ctx_enable_counters": (_i, [_vp, _i]),
     "mp_counters": (_i, [_vp, _P(MpCounters)]),

@@ -6,6 +6,7 @@
 #include "host_common.h"
 #include "kernels.cuh"
 #include "wavefront.cuh"
+#include "octet.cuh"
 #include "probes.cuh"
 
 using namespace mp;
@@ -28,6 +29,11 @@ struct MpCtx {
     // scene
     void* d_scene_blob = nullptr;
     mpd::Scene scene{};
+    mpd::SceneCM scene_cm{};
+    uint32_t trace_variant = MP_TRACE_OCTET;
+    int sm_count = 148;
+    int octet_bps = 0;
+    size_t octet_bps_smem = 0;
     bool has_scene = false;
     uint32_t max_stack = 0;
     // camera
@@ -134,6 +140,7 @@ int mp_ctx_create(int device, MpCtx** out) {
     if (prop.major != 10) return fail(MP_ENODEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
     MpCtx* ctx = new MpCtx();
     ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
     ctx->stream = ctx->own_stream;
     CK(cudaEventCreate(&ctx->ev0));
@@ -167,6 +174,13 @@ int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream) {
     if (int rc = use_device(ctx)) return rc;
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    return MP_OK;
+}
+
+int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant) {
+    if (!ctx) return fail(MP_EINVAL, "null context");
+    if (variant > MP_TRACE_OCTET) return fail(MP_EINVAL, "bad trace variant %u", variant);
+    ctx->trace_variant = variant;
     return MP_OK;
 }
 
@@ -217,7 +231,7 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     if (b->n_packets == 0) return fail(MP_EINVAL, "scene has no triangle packets");
     MpBvhStats st;
     if (int rc = mp_bvh_stats(b, &st)) return rc;
-    if (st.max_stack > MPD_STACK_MAX) return fail(MP_EINVAL, "BVH depth %u needs a %u-entry stack (limit %d)", st.max_depth, st.max_stack, MPD_STACK_MAX);
+    if (st.max_stack > MPD_OCTET_STACK_MAX) return fail(MP_EINVAL, "BVH depth %u needs a %u-entry stack (limit %d)", st.max_depth, st.max_stack, MPD_OCTET_STACK_MAX);
     CK(cudaStreamSynchronize(ctx->stream));
     if (ctx->d_scene_blob) CK(cudaFree(ctx->d_scene_blob));
     ctx->d_scene_blob = nullptr;
@@ -226,7 +240,7 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     const size_t s_inner = al((size_t)b->n_inner * sizeof(MpInnerNode)), s_ibox = al((size_t)b->n_inner * sizeof(MpBox));
     const size_t s_pack = al((size_t)b->n_packets * sizeof(MpTrianglePacket)), s_pbox = al((size_t)b->n_packets * sizeof(MpBox));
     const size_t s_sh = al((size_t)b->n_packets * 8 * sizeof(MpTriShading)), s_v = al((size_t)b->n_vertices * sizeof(MpVertexShading));
-    const size_t total = s_inner + s_ibox + s_pack + s_pbox + s_sh + s_v + 256;
+    const size_t total = 2 * s_inner + s_ibox + 2 * s_pack + s_pbox + s_sh + s_v + 256;
     CK(cudaMalloc(&ctx->d_scene_blob, total));
     char* p = (char*)ctx->d_scene_blob;
     auto up = [&](const void* src, size_t bytes, size_t slot) -> const void* {
@@ -241,6 +255,31 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     ctx->scene.packet_box = (const float4*)up(b->packet_box, (size_t)b->n_packets * sizeof(MpBox), s_pbox);
     ctx->scene.tri_shading = (const uint4*)up(b->tri_shading, (size_t)b->n_packets * 8 * sizeof(MpTriShading), s_sh);
     ctx->scene.vertices = (const float4*)up(b->vertices, (size_t)b->n_vertices * sizeof(MpVertexShading), s_v);
+    // child-major copies for the octet kernels (octet.cuh): one 16-byte record per child / per triangle
+    std::vector<uint32_t> cm_inner((size_t)b->n_inner * 32), cm_pack((size_t)b->n_packets * 36);
+    for (size_t i = 0; i < b->n_inner; ++i) {
+        const MpInnerNode& nd = b->inner[i];
+        for (int k = 0; k < 8; ++k) {
+            uint32_t* o = &cm_inner[i * 32 + k * 4];
+            o[0] = nd.bounds[0][k] | (uint32_t)nd.bounds[1][k] << 16;
+            o[1] = nd.bounds[2][k] | (uint32_t)nd.bounds[3][k] << 16;
+            o[2] = nd.bounds[4][k] | (uint32_t)nd.bounds[5][k] << 16;
+            o[3] = nd.links[k];
+        }
+    }
+    for (size_t i = 0; i < b->n_packets; ++i) {
+        const MpTrianglePacket& pk = b->packets[i];
+        for (int k = 0; k < 8; ++k) {
+            uint32_t* o = &cm_pack[i * 36 + k * 4];
+            o[0] = pk.v[0][0][k] | (uint32_t)pk.v[0][1][k] << 16;
+            o[1] = pk.v[0][2][k] | (uint32_t)pk.v[1][0][k] << 16;
+            o[2] = pk.v[1][1][k] | (uint32_t)pk.v[1][2][k] << 16;
+            o[3] = pk.v[2][0][k] | (uint32_t)pk.v[2][1][k] << 16;
+        }
+        for (int w = 0; w < 4; ++w) cm_pack[i * 36 + 32 + w] = pk.v[2][2][2 * w] | (uint32_t)pk.v[2][2][2 * w + 1] << 16;
+    }
+    ctx->scene_cm.inner_cm = (const uint4*)up(cm_inner.data(), cm_inner.size() * 4, s_inner);
+    ctx->scene_cm.packets_cm = (const uint4*)up(cm_pack.data(), cm_pack.size() * 4, s_pack);
     ctx->scene.root = b->root;
     {  // extension integrator epsilon: 1e-4 * |bbox size|, same unfused arithmetic as the oracle
         V3 s = v3(b->bbox_max[0], b->bbox_max[1], b->bbox_max[2]) - v3(b->bbox_min[0], b->bbox_min[1], b->bbox_min[2]);

@@ -1,0 +1,290 @@
+// BVH8 traversal with EIGHT LANES PER RAY ("octet"): lane k of an octet owns child k of an inner node and triangle k of
+// a packet, so the reference's 8-wide f32x8 arithmetic (src/scene/triangle_bvh/ray_bvh_intersection.rs:104-162,
+// src/geometry/aabb.rs:257-283, src/geometry/triangle.rs:187-216) maps lane for lane onto 8 CUDA threads and a warp
+// carries 4 rays.  Same visiting order and same per-lane arithmetic as trace.cuh (thread per ray), hence the same bits;
+// what changes is the execution shape: divergence is per octet instead of per thread, each octet refills itself with the
+// next ray as soon as its stack runs empty, and the per-ray stack lives in shared memory (8-byte entries).
+//
+// Device layout read here ("child-major", built from MpFlatBvh at upload; one 128-bit load per lane):
+//   inner_cm[i*8+k]   uint4 { min.x|min.y<<16, min.z|max.x<<16, max.y|max.z<<16, link }   child k of node i
+//   packets_cm[p*9+k] uint4 { v0.x|v0.y<<16, v0.z|v1.x<<16, v1.y|v1.z<<16, v2.x|v2.y<<16 } triangle k of packet p
+//   packets_cm[p*9+8] 8 x u16 v2.z of the 8 triangles
+//   inner_box / packet_box as in trace.cuh.
+#pragma once
+#include "wavefront.cuh"
+
+namespace mpd {
+
+struct SceneCM {
+    const uint4* __restrict__ inner_cm;
+    const uint4* __restrict__ packets_cm;
+};
+
+__device__ __forceinline__ float unit_rel_lo(uint32_t w) {
+    return __fmaf_rn(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7410)), MPD_K_INV_U16, -8388608.0f * MPD_K_INV_U16);
+}
+__device__ __forceinline__ float unit_rel_hi(uint32_t w) {
+    return __fmaf_rn(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7432)), MPD_K_INV_U16, -8388608.0f * MPD_K_INV_U16);
+}
+
+// One lane's share of InnerNode::intersect (same expressions as child_slab in trace.cuh).
+template <bool NANPATH>
+__device__ __forceinline__ bool octet_child_slab(const uint4 c, const F3& bmin, const F3& bsize, const Ray& r, float max_t, float& t1_out) {
+    float lox = __fmul_rn(__fsub_rn(__fmaf_rn(bsize.x, unit_rel_lo(c.x), bmin.x), r.o.x), r.inv.x);
+    float loy = __fmul_rn(__fsub_rn(__fmaf_rn(bsize.y, unit_rel_hi(c.x), bmin.y), r.o.y), r.inv.y);
+    float loz = __fmul_rn(__fsub_rn(__fmaf_rn(bsize.z, unit_rel_lo(c.y), bmin.z), r.o.z), r.inv.z);
+    float hix = __fmul_rn(__fsub_rn(__fmaf_rn(bsize.x, unit_rel_hi(c.y), bmin.x), r.o.x), r.inv.x);
+    float hiy = __fmul_rn(__fsub_rn(__fmaf_rn(bsize.y, unit_rel_lo(c.z), bmin.y), r.o.y), r.inv.y);
+    float hiz = __fmul_rn(__fsub_rn(__fmaf_rn(bsize.z, unit_rel_hi(c.z), bmin.z), r.o.z), r.inv.z);
+    float t1, t2;
+    if (NANPATH) {
+        if (lox != lox) lox = MPD_NINF;
+        if (loy != loy) loy = MPD_NINF;
+        if (loz != loz) loz = MPD_NINF;
+        if (hix != hix) hix = MPD_INF;
+        if (hiy != hiy) hiy = MPD_INF;
+        if (hiz != hiz) hiz = MPD_INF;
+        float cminx = minps(lox, hix), cminy = minps(loy, hiy), cminz = minps(loz, hiz);
+        float cmaxx = maxps(lox, hix), cmaxy = maxps(loy, hiy), cmaxz = maxps(loz, hiz);
+        t1 = maxps(maxps(cminx, 0.0f), maxps(cminy, cminz));
+        t2 = minps(minps(cmaxx, max_t), minps(cmaxy, cmaxz));
+    } else {
+        float cminx = fminf(lox, hix), cminy = fminf(loy, hiy), cminz = fminf(loz, hiz);
+        float cmaxx = fmaxf(lox, hix), cmaxy = fmaxf(loy, hiy), cmaxz = fmaxf(loz, hiz);
+        t1 = fmaxf(fmaxf(cminx, 0.0f), fmaxf(cminy, cminz));
+        t2 = fminf(fminf(cmaxx, max_t), fminf(cmaxy, cmaxz));
+    }
+    t1_out = t1;
+    return t1 <= t2;
+}
+
+// One lane's triangle of a packet (same expressions as tri_lane in trace.cuh).
+__device__ __forceinline__ bool octet_tri(const uint4 a, uint32_t v2z_word, bool odd, const F3& bmin, const F3& bsize, const Ray& r,
+                                          float max_t, float& t_out, float& u_out, float& v_out) {
+    const F3 v0 = f3(__fmaf_rn(bsize.x, unit_rel_lo(a.x), bmin.x), __fmaf_rn(bsize.y, unit_rel_hi(a.x), bmin.y), __fmaf_rn(bsize.z, unit_rel_lo(a.y), bmin.z));
+    const F3 v1 = f3(__fmaf_rn(bsize.x, unit_rel_hi(a.y), bmin.x), __fmaf_rn(bsize.y, unit_rel_lo(a.z), bmin.y), __fmaf_rn(bsize.z, unit_rel_hi(a.z), bmin.z));
+    const float z2 = odd ? unit_rel_hi(v2z_word) : unit_rel_lo(v2z_word);
+    const F3 v2 = f3(__fmaf_rn(bsize.x, unit_rel_lo(a.w), bmin.x), __fmaf_rn(bsize.y, unit_rel_hi(a.w), bmin.y), __fmaf_rn(bsize.z, z2, bmin.z));
+    const F3 e1 = v1 - v0, e2 = v2 - v0;
+    const F3 p = fma_cross(r.d, e2);
+    const float det = fma_dot(e1, p);
+    const float inv = __fdiv_rn(1.0f, det);
+    const F3 s = r.o - v0;
+    const float u = __fmul_rn(inv, fma_dot(s, p));
+    const F3 qv = fma_cross(s, e1);
+    const float v = __fmul_rn(inv, fma_dot(r.d, qv));
+    const float t = __fmul_rn(inv, fma_dot(e2, qv));
+    t_out = t, u_out = u, v_out = v;
+    return u >= 0.0f && v >= 0.0f && __fadd_rn(u, v) <= 1.0f && t >= 0.0f && t <= max_t;
+}
+
+struct OctetLane {
+    uint32_t sub;    // lane within the octet: child / triangle index
+    uint32_t shift;  // first warp lane of the octet (0, 8, 16, 24)
+    uint32_t mask;   // warp lane mask of the octet
+};
+__device__ __forceinline__ OctetLane octet_lane() {
+    const uint32_t l = threadIdx.x & 31u;
+    return OctetLane{l & 7u, l & 24u, 0xFFu << (l & 24u)};
+}
+
+// One traversal step of one octet: pop the top entry and process it (inner node or leaf).  All 8 lanes hold identical
+// copies of (r, best, sp).  `stk` is the octet's shared-memory stack.  Returns with sp == 0 when the ray is finished.
+template <int ORDER, bool COUNT, bool NANPATH>
+__device__ __forceinline__ void octet_step(const Scene& sc, const SceneCM& cm, const OctetLane& ol, const Ray& r, bool any_hit,
+                                           uint2* __restrict__ stk, int& sp, Hit& best, Visits& vis) {
+    __syncwarp(ol.mask);  // entries written by sibling lanes in the previous step are visible
+    const uint2 e = stk[--sp];
+    if (__uint_as_float(e.y) > best.t) return;  // ray_bvh_intersection.rs:40
+    const uint32_t count = e.x & MP_LINK_COUNT_MASK, index = e.x >> MP_LINK_COUNT_BITS;
+    if (count == 0) {
+        // ---- inner node: lane k tests child k (ray_bvh_intersection.rs:149-162) ----
+        if (COUNT) vis.inner++;
+        const float4 b0 = __ldg(sc.inner_box + 2 * (size_t)index), b1 = __ldg(sc.inner_box + 2 * (size_t)index + 1);
+        const uint4 c = __ldg(cm.inner_cm + 8 * (size_t)index + ol.sub);
+        float t1;
+        bool hit = octet_child_slab<NANPATH>(c, f3(b0.x, b0.y, b0.z), f3(b1.x, b1.y, b1.z), r, best.t, t1);
+        hit = hit && c.w != MP_LINK_NULL;  // NULL children are discarded when popped (:49); skipping them is neutral
+        const uint32_t hits = (__ballot_sync(ol.mask, hit) >> ol.shift) & 0xFFu;
+        uint32_t pos;
+        if (ORDER == MP_ORDER_NEAR_FIRST) {
+            // far → near from the base; ties: lower lane nearer the top (same final order as the insertion in trace.cuh)
+            pos = 0;
+#pragma unroll
+            for (int k = 1; k < 8; ++k) {
+                const uint32_t j = (ol.sub + k) & 7u;
+                const float tj = __shfl_sync(ol.mask, t1, ol.shift + j);
+                if (((hits >> j) & 1u) && (tj > t1 || (tj == t1 && j > ol.sub))) ++pos;
+            }
+        } else {
+            pos = __popc(hits & ((1u << ol.sub) - 1u));  // lane order: lane 7 pops first (:161)
+        }
+        if (hit) stk[sp + pos] = make_uint2(c.w, __float_as_uint(t1));
+        sp += __popc(hits);
+    } else {
+        // ---- leaf: packets in order, lane k tests triangle k of each (ray_bvh_intersection.rs:104-141) ----
+        if (COUNT) vis.leaves++, vis.packets += count;
+        const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)index), b1 = __ldg(sc.packet_box + 2 * (size_t)index + 1);
+        const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
+        const float max_t = best.t;  // not updated inside the leaf
+        Hit local{MPD_INF, 0.0f, 0.0f, MP_NO_HIT};
+        for (uint32_t j = 0; j < count; ++j) {
+            const uint4* pk = cm.packets_cm + 9 * (size_t)(index + j);
+            const uint4 a = __ldg(pk + ol.sub);
+            const uint32_t zw = __ldg(reinterpret_cast<const uint32_t*>(pk + 8) + (ol.sub >> 1));
+            float t, u, v;
+            const bool valid = octet_tri(a, zw, ol.sub & 1u, bmin, bsize, r, max_t, t, u, v);
+            // first minimum over the 8 lanes in lane order (:127-135): min of t, then the lowest lane that attains it
+            const float key = valid ? t : MPD_INF;
+            float m = fminf(key, __shfl_xor_sync(ol.mask, key, 1));
+            m = fminf(m, __shfl_xor_sync(ol.mask, m, 2));
+            m = fminf(m, __shfl_xor_sync(ol.mask, m, 4));
+            const uint32_t eq = (__ballot_sync(ol.mask, valid && key == m) >> ol.shift) & 0xFFu;
+            if (eq) {  // uniform within the octet
+                const uint32_t win = __ffs(eq) - 1u;
+                const float tw = __shfl_sync(ol.mask, t, ol.shift + win);
+                const float uw = __shfl_sync(ol.mask, u, ol.shift + win);
+                const float vw = __shfl_sync(ol.mask, v, ol.shift + win);
+                if (tw < local.t) local = Hit{tw, uw, vw, (index + j) * 8u + win};
+            }
+        }
+        if (local.t < best.t) {  // :59
+            best = local;
+            if (any_hit) sp = 0;
+        }
+    }
+}
+
+// Drives one octet over rays i = first, first + stride, … < n.  fetch(i, r) loads ray i (all 8 lanes, identical values);
+// emit(i, best) is called by every lane of the octet when ray i is finished (lane sub == 0 should do the store).
+template <int ORDER, bool COUNT, class Fetch, class Emit>
+__device__ __forceinline__ void octet_run(const Scene& sc, const SceneCM& cm, uint32_t n, uint32_t first, uint32_t stride, bool any_hit,
+                                          uint2* __restrict__ stk, Fetch fetch, Emit emit, ThreadCounts& tc) {
+    const OctetLane ol = octet_lane();
+    uint32_t cur = 0, next = first;
+    bool have = false, nanpath = false;
+    int sp = 0;
+    Ray r;
+    Hit best{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
+    for (;;) {
+        if (sp == 0) {
+            if (have) {
+                emit(cur, best);
+                have = false;
+            }
+            if (next < n) {
+                cur = next, next += stride;
+                fetch(cur, r);
+                nanpath = (fabsf(r.inv.x) == MPD_INF) | (fabsf(r.inv.y) == MPD_INF) | (fabsf(r.inv.z) == MPD_INF);
+                best = Hit{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
+                if (ol.sub == 0) stk[0] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
+                sp = 1;
+                have = true;
+                tc.rays++;
+            }
+        }
+        if (!have) break;  // this octet has no more rays; lanes of other octets keep going (octet-scoped sync only)
+        if (nanpath)
+            octet_step<ORDER, COUNT, true>(sc, cm, ol, r, any_hit, stk, sp, best, tc.vis);
+        else
+            octet_step<ORDER, COUNT, false>(sc, cm, ol, r, any_hit, stk, sp, best, tc.vis);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// kernels: 128 threads = 16 octets per block; dynamic shared memory = 16 stacks of stack_cap 8-byte entries
+// ---------------------------------------------------------------------------------------------------------------
+#define OCTETS_PER_BLOCK 16
+
+__device__ __forceinline__ void octet_finish_counts(DevCounters* dc, ThreadCounts& tc, bool count_visits) {
+    if ((threadIdx.x & 7u) != 0) tc = ThreadCounts{};  // the 8 lanes of an octet counted the same ray
+    flush_counts(dc, tc, count_visits);
+}
+
+// inv_direction as Ray::new computes it (geometry/mod.rs:47), one division per lane instead of three
+__device__ __forceinline__ void octet_inv(const OctetLane& ol, Ray& r) {
+    const uint32_t a = ol.sub % 3u;
+    const float dc = a == 0 ? r.d.x : (a == 1 ? r.d.y : r.d.z);
+    const float ic = dc == 0.0f ? MPD_INF : __fdiv_rn(1.0f, dc);
+    r.inv.x = __shfl_sync(ol.mask, ic, ol.shift + 0);
+    r.inv.y = __shfl_sync(ol.mask, ic, ol.shift + 1);
+    r.inv.z = __shfl_sync(ol.mask, ic, ol.shift + 2);
+}
+
+// Object::intersect on caller-provided rays (the bit-exactness gate), octet variant.
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) trace_rays_octet_kernel(Scene sc, SceneCM cm, const float* __restrict__ rays, uint32_t n,
+                                                               uint4* __restrict__ hits, DevCounters* dc, uint32_t stack_cap) {
+    extern __shared__ uint2 octet_stacks[];
+    uint2* stk = octet_stacks + (threadIdx.x >> 3) * stack_cap;
+    ThreadCounts tc{};
+    octet_run<ORDER, COUNT>(
+        sc, cm, n, blockIdx.x * OCTETS_PER_BLOCK + (threadIdx.x >> 3), gridDim.x * OCTETS_PER_BLOCK, false, stk,
+        [&](uint32_t i, Ray& r) {
+            const float* p = rays + 9 * (size_t)i;
+            r.o = f3(__ldg(p + 0), __ldg(p + 1), __ldg(p + 2));
+            r.d = f3(__ldg(p + 3), __ldg(p + 4), __ldg(p + 5));
+            r.inv = f3(__ldg(p + 6), __ldg(p + 7), __ldg(p + 8));
+        },
+        [&](uint32_t i, const Hit& h) {
+            if ((threadIdx.x & 7u) == 0) hits[i] = make_uint4(h.tri, __float_as_uint(h.t), __float_as_uint(h.u), __float_as_uint(h.v));
+        },
+        tc);
+    octet_finish_counts(dc, tc, COUNT);
+}
+
+// Wavefront stage 2 (closest hit), octet variant of wf_trace_kernel.
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) wf_trace_octet_kernel(Scene sc, SceneCM cm, const uint32_t* __restrict__ queue,
+                                                             const uint32_t* __restrict__ count, const float4* __restrict__ ray_o,
+                                                             const float4* __restrict__ ray_d, uint4* __restrict__ hit, DevCounters* dc,
+                                                             uint32_t stack_cap) {
+    extern __shared__ uint2 octet_stacks[];
+    uint2* stk = octet_stacks + (threadIdx.x >> 3) * stack_cap;
+    const OctetLane ol = octet_lane();
+    ThreadCounts tc{};
+    uint32_t path = 0;
+    octet_run<ORDER, COUNT>(
+        sc, cm, *count, blockIdx.x * OCTETS_PER_BLOCK + (threadIdx.x >> 3), gridDim.x * OCTETS_PER_BLOCK, false, stk,
+        [&](uint32_t i, Ray& r) {
+            path = queue[i];
+            const float4 o = ray_o[path], d = ray_d[path];
+            r.o = f3(o.x, o.y, o.z), r.d = f3(d.x, d.y, d.z);
+            octet_inv(ol, r);
+        },
+        [&](uint32_t, const Hit& h) {
+            if (ol.sub == 0) hit[path] = make_uint4(h.tri, __float_as_uint(h.t), __float_as_uint(h.u), __float_as_uint(h.v));
+        },
+        tc);
+    octet_finish_counts(dc, tc, COUNT);
+}
+
+// Wavefront stage 3b (any hit towards the sun), octet variant of wf_shadow_kernel.
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) wf_shadow_octet_kernel(Scene sc, SceneCM cm, const float4* __restrict__ sh_o,
+                                                              const uint32_t* __restrict__ sh_path, const uint32_t* __restrict__ sh_count,
+                                                              float4* __restrict__ ray_d, DevCounters* dc, uint32_t stack_cap) {
+    extern __shared__ uint2 octet_stacks[];
+    uint2* stk = octet_stacks + (threadIdx.x >> 3) * stack_cap;
+    const OctetLane ol = octet_lane();
+    ThreadCounts tc{};
+    float contribution = 0.0f;
+    octet_run<ORDER, COUNT>(
+        sc, cm, *sh_count, blockIdx.x * OCTETS_PER_BLOCK + (threadIdx.x >> 3), gridDim.x * OCTETS_PER_BLOCK, true, stk,
+        [&](uint32_t i, Ray& r) {
+            const float4 o = sh_o[i];
+            contribution = o.w;
+            r = ray_new(f3(o.x, o.y, o.z), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
+            tc.shadow_rays++;
+        },
+        [&](uint32_t i, const Hit& h) {
+            if (ol.sub == 0 && h.tri == MP_NO_HIT) {
+                const uint32_t path = sh_path[i];
+                ray_d[path].w = __fadd_rn(ray_d[path].w, contribution);
+            }
+        },
+        tc);
+    octet_finish_counts(dc, tc, COUNT);
+}
+
+}  // namespace mpd

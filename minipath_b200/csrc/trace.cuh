@@ -15,7 +15,8 @@
 
 namespace mpd {
 
-#define MPD_STACK_MAX 64
+#define MPD_STACK_MAX 128        // thread-per-ray variant: local-memory stack
+#define MPD_OCTET_STACK_MAX 384  // octet variant: shared-memory stack, 16 octets x cap x 8 B per block
 
 struct Scene {
     const uint4* __restrict__ inner;

@@ -192,3 +192,41 @@ def test_full_size_properties(gpu_ctx, teapot, teapot_camera):
     assert np.all(film[..., 0] <= a + 1e-4) and np.all(film[..., 0] == film[..., 1]) and np.all(film[..., 1] == film[..., 2])
     assert 0.15 < (a > 0).mean() < 0.6  # the teapot covers a good part of the frame
     assert a[:50].sum() == 0 and a[-50:].sum() == 0  # top/bottom rows are background
+
+
+def test_atrium_standin_bit_exact(gpu_ctx, oracle):
+    """Sponza STAND-IN (263 k triangles, reference split: depth 16, 106-entry stack): primary rays from its camera plus
+    incoherent rays, hits bit-exact; a small 5-bounce wavefront film bit-exact."""
+    from minipath_b200 import scenes
+
+    bvh, cam = scenes.atrium_scene()
+    w, h = 192, 108
+    s = _setup(gpu_ctx, bvh, cam, w, h)
+    st = mp.RenderSettings(64, 2, (w, h), seed=321, max_bounces=5, mode=mp.MODE_WAVEFRONT)
+    tiles = mp.full_screen_tiles(w, h, 64, seed=2)
+    rays = oracle.generate_rays(s, w, tiles, st.params())
+    lo, hi = bvh.get_bounding_box()
+    o, d = scenes.incoherent_rays(lo, hi, 30000)
+    rays = np.concatenate([rays, oracle.rays_from(o, d)])
+    for order in (mp.ORDER_REFERENCE, mp.ORDER_NEAR_FIRST):
+        h_cpu = oracle.trace_rays(bvh, rays, order)
+        assert (h_cpu["tri"] != mp.NO_HIT).mean() > 0.8  # an interior view: most rays hit something
+        _assert_hits_equal(gpu_ctx.trace_rays(rays, order), h_cpu)
+    gpu_ctx.render_tiles(tiles, st.params())
+    film_cpu, _, _ = oracle.render_tiles(bvh, s, w, h, tiles, st.params())
+    assert np.array_equal(_bits(gpu_ctx.read_film()), _bits(film_cpu))
+
+
+def test_soup_median_builder_bit_exact(gpu_ctx, oracle):
+    """BASELINE.json configs[4] in small: 100 k random triangles, median-split builder (same node format), incoherent rays."""
+    from minipath_b200 import scenes
+
+    pos, tri = scenes.soup_mesh(100_000)
+    bvh = mp.TriangleBvh.from_mesh(pos, tri, builder=1)
+    gpu_ctx.upload_scene(bvh)
+    lo, hi = bvh.get_bounding_box()
+    o, d = scenes.incoherent_rays(lo, hi, 50000)
+    rays = oracle.rays_from(o, d)
+    h_cpu = oracle.trace_rays(bvh, rays, mp.ORDER_REFERENCE)
+    assert 0.2 < (h_cpu["tri"] != mp.NO_HIT).mean()
+    _assert_hits_equal(gpu_ctx.trace_rays(rays, mp.ORDER_REFERENCE), h_cpu)
