@@ -47,9 +47,9 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="teapot-1080p", choices=sorted(WORKLOADS))
-    ap.add_argument("--mode", default="auto", choices=["auto", "megakernel", "wavefront", "wavefront-thread"],
-                    help="megakernel: one thread per pixel; wavefront: staged kernels with the octet traversal kernel; "
-                         "wavefront-thread: staged kernels with the thread-per-ray traversal kernel")
+    ap.add_argument("--mode", default="auto", choices=["auto", "megakernel", "wavefront-octet", "wavefront-thread", "wavefront-persist"],
+                    help="megakernel: one thread per pixel; wavefront-*: staged kernels with the thread-per-ray, the 8-lanes-per-ray "
+                         "(octet) or the persistent phased thread-per-ray traversal kernel")
     ap.add_argument("--order", default="reference", choices=["reference", "near_first"])
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel")
     ap.add_argument("--bounces", type=int, default=-1, help="override the workload's max_bounces")
@@ -236,7 +236,12 @@ def run_b200(args, rank, local, world):
     def reduce_fn(t):
         dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
 
-    modes = {"megakernel": mp.MODE_MEGAKERNEL, "wavefront": mp.MODE_WAVEFRONT, "wavefront-thread": mp.MODE_WAVEFRONT}
+    modes = {"megakernel": mp.MODE_MEGAKERNEL, "wavefront-thread": mp.MODE_WAVEFRONT, "wavefront-octet": mp.MODE_WAVEFRONT,
+             "wavefront-persist": mp.MODE_WAVEFRONT}
+    variants = {"megakernel": mp.TRACE_THREAD, "wavefront-thread": mp.TRACE_THREAD, "wavefront-octet": mp.TRACE_OCTET,
+                "wavefront-persist": mp.TRACE_PERSIST}
+    if bvh.stats()["max_stack"] > 128:  # deeper than the local-memory stack of the thread-per-ray kernels
+        modes = {"wavefront-octet": mp.MODE_WAVEFRONT}
 
     def make_step(mode_key):
         mode = modes[mode_key]
@@ -246,7 +251,7 @@ def run_b200(args, rank, local, world):
             ctx.render_tiles(sub_tiles, st.params(sample_base=base))
 
         def step():
-            ctx.set_trace_variant(mp.TRACE_THREAD if mode_key == "wavefront-thread" else mp.TRACE_OCTET)
+            ctx.set_trace_variant(variants[mode_key])
             film.zero_()
             # weak scaling: every rank renders the full frame with its own `spp` sample indices; total spp = spp * world
             mpdist.render_sharded(render_fn, film, tiles, spp * world if args.shard == "spp" else spp, rank, world, args.shard,
@@ -328,7 +333,7 @@ def run_b200(args, rank, local, world):
 
     res = dict(ctx=ctx, bvh=bvh, cam=cam, w=w, h=h, spp=spp, bounces=bounces, tiles=tiles, cnt=cnt, ab=ab, mode_name=mode_name,
                ms_per_step=ms_per_step, value=value, samples_per_s=samples_job / (ms_per_step * 1e-3), clocks=clocks,
-               launches=launches, rays_job=rays_job, stream=stream, torch=torch, dist=dist, modes=modes, order=order, barrier=barrier)
+               launches=launches, rays_job=rays_job, stream=stream, torch=torch, dist=dist, modes=modes, variants=variants, order=order, barrier=barrier)
     return res
 
 
@@ -345,7 +350,7 @@ def run_e2e(args, res, rank, local, world):
     n_tiles = len(res["tiles"])
     mode = res["modes"][res["mode_name"]]
     if world == 1:
-        st = mp.RenderSettings(64, spp, (w, h), max_bounces=bounces, seed=7, mode=mode, order=res["order"])
+        st = mp.RenderSettings(64, spp, (w, h), max_bounces=bounces, seed=7, mode=mode, order=res["order"], trace_kernel=res["variants"][res["mode_name"]])
 
         def once():
             prog = mp.render(mp.Scene(bvh), cam, st, devices=[local])
@@ -415,8 +420,9 @@ def roofline(args, res):
         out = {"bound": mem_bound[0], "achieved": bytes_ / secs / 1e9, "peak": mem_bound[2], "unit": "GB/s", "frac": mem_bound[1] / secs}
     out.update({
         "traffic": None,
-        "kernel": {"megakernel": "render_mega_kernel", "wavefront": "wf_trace_octet_kernel+wf_shadow_octet_kernel",
-                   "wavefront-thread": "wf_trace_kernel+wf_shadow_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
+        "kernel": {"megakernel": "render_mega_kernel", "wavefront-octet": "wf_trace_octet_kernel+wf_shadow_octet_kernel",
+                   "wavefront-thread": "wf_trace_kernel+wf_shadow_kernel",
+                   "wavefront-persist": "wf_trace_persist_kernel+wf_shadow_persist_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
         "peak_source": "FP32 FMA and L2 read bandwidth measured by mp_probe_* in this run; HBM " + hbm_src,
         "fp32": {"achieved_tflops": flops / secs / 1e12, "peak_tflops": fp32, "frac": t_fp32 / secs},
         "l2": {"achieved_gbs": bytes_ / secs / 1e9, "peak_gbs": l2, "frac": t_l2 / secs},

@@ -202,14 +202,21 @@ const char* mp_last_error(void);
 int mp_device_count(int* out);
 int mp_ctx_create(int device, MpCtx** out);
 int mp_ctx_destroy(MpCtx* ctx);
+/* Process-wide pool of idle contexts (streams, film, path-state and staging buffers stay allocated between renders).
+ * mp_render() takes its per-device worker contexts from here. */
+int mp_ctx_pool_acquire(int device, MpCtx** out);
+int mp_ctx_pool_release(MpCtx* ctx);
+int mp_ctx_pool_clear(void);
 /* Run on a caller-owned CUDA stream (cudaStream_t as void*); NULL → the context's own stream. */
 int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream);
 int mp_ctx_sync(MpCtx* ctx);
 /* Which traversal kernel serves mp_trace_rays* and the wavefront pipeline (same visiting order, same bits):
- * THREAD = one thread per ray, SoA node rows, local-memory stack (trace.cuh);
- * OCTET  = eight lanes per ray, child-major 16-byte records, shared-memory stack, self-refilling octets (octet.cuh; default). */
+ * THREAD = one thread per ray, SoA node rows, local-memory stack (trace.cuh; default);
+ * OCTET  = eight lanes per ray, child-major 16-byte records, shared-memory stack, self-refilling octets (octet.cuh). */
 #define MP_TRACE_THREAD 0u
 #define MP_TRACE_OCTET 1u
+/* PERSIST = one thread per ray, persistent lanes that refill themselves, warp-voted inner / packet phases (persist.cuh) */
+#define MP_TRACE_PERSIST 2u
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant);
 /* Count traversal work (adds a few atomics per warp); off by default. */
 int mp_ctx_enable_counters(MpCtx* ctx, int on);
@@ -238,6 +245,15 @@ int mp_film_device_ptr(MpCtx* ctx, void** out);
 /* Worker::render_tile for n tiles at once (worker.rs:32-49): accumulates sample_count samples per pixel
  * into the film, sequentially per pixel in sample order.  Asynchronous on the context's stream. */
 int mp_render_tiles(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, const MpRenderParams* params);
+/* The render's whole tile_ordering kept on the device (RenderState::tile_ordering, machinery.rs:36-41); batches are then
+ * addressed by index range, like the workers' `next_tile_index` (machinery.rs:205-209).  Asynchronous. */
+int mp_tiles_upload(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, uint32_t tile_size);
+int mp_render_tile_range(MpCtx* ctx, uint32_t first, uint32_t n_tiles, const MpRenderParams* params);
+/* Tile-packed RGBA8 read-back of a range, double-buffered (slot 0/1): _begin queues resolve + copy into pinned host
+ * memory, _end waits for that slot and returns the buffer [n_tiles][tile_size][tile_size] (valid until the slot is reused).
+ * Lets the next batch render while the previous one is copied into the image (machinery.rs:78-89). */
+int mp_film_resolve_tiles_begin(MpCtx* ctx, uint32_t first, uint32_t n_tiles, uint32_t tile_size, uint32_t spp_total, int slot);
+int mp_film_resolve_tiles_end(MpCtx* ctx, int slot, const uint8_t** host_tiles);
 /* pixel_sum * (1/spp) then color_to_image (worker.rs:44,69-76) for the whole film → host RGBA8. Synchronises. */
 int mp_film_resolve_rgba8(MpCtx* ctx, uint32_t spp_total, uint8_t* host_out);
 /* Same, into caller-owned device memory (width*height RGBA8 words); asynchronous on the context's stream. */
@@ -274,6 +290,8 @@ typedef struct MpRenderSettings { /* renderer/mod.rs:7-13 + extension fields wit
     uint32_t mode;        /* MP_MODE_* */
     uint32_t order;       /* MP_ORDER_* */
     uint32_t tiles_per_batch; /* 0 → default */
+    uint32_t trace_kernel;    /* 0 → chosen by the library; otherwise MP_TRACE_* + 1 */
+    uint32_t _pad;
     uint64_t seed;        /* 0 → OS-random like SmallRng::from_os_rng (worker.rs:25) */
 } MpRenderSettings;
 typedef struct MpProgressSnapshot { size_t finished, total; } MpProgressSnapshot; /* machinery.rs:180-183 */

@@ -18,6 +18,7 @@ from ._ffi import (  # noqa: F401  (re-exported)
     ORDER_NEAR_FIRST,
     ORDER_REFERENCE,
     TRACE_OCTET,
+    TRACE_PERSIST,
     TRACE_THREAD,
     MpError,
     check,
@@ -196,17 +197,18 @@ class RenderSettings:
     """renderer/mod.rs:7-13 plus extension fields whose defaults reproduce the reference (0 bounces, OS seed)."""
 
     def __init__(self, tile_size, sample_count, resolution, max_bounces=0, seed=0, mode=MODE_MEGAKERNEL, order=ORDER_REFERENCE,
-                 tiles_per_batch=0):
+                 tiles_per_batch=0, trace_kernel=None):
         if tile_size <= 0 or sample_count <= 0:
             raise ValueError("tile_size and sample_count are NonZeroU32")
         self.tile_size, self.sample_count = int(tile_size), int(sample_count)
         self.resolution = (int(resolution[0]), int(resolution[1]))
         self.max_bounces, self.seed, self.mode, self.order = int(max_bounces), int(seed), int(mode), int(order)
         self.tiles_per_batch = int(tiles_per_batch)
+        self.trace_kernel = trace_kernel  # None: chosen by the library; else TRACE_THREAD / TRACE_OCTET / TRACE_PERSIST
 
     def _raw(self):
         return _ffi.MpRenderSettings(self.tile_size, self.sample_count, self.resolution[0], self.resolution[1], self.max_bounces, self.mode,
-                                     self.order, self.tiles_per_batch, self.seed)
+                                     self.order, self.tiles_per_batch, 0 if self.trace_kernel is None else self.trace_kernel + 1, 0, self.seed)
 
     def params(self, sample_count=None, sample_base=0):
         return _ffi.MpRenderParams(self.sample_count if sample_count is None else sample_count, sample_base, self.max_bounces, self.mode,

@@ -18,7 +18,7 @@ NO_HIT = 0xFFFFFFFF
 TRI_FLAT = 0x80000000
 MODE_MEGAKERNEL, MODE_WAVEFRONT = 0, 1
 ORDER_REFERENCE, ORDER_NEAR_FIRST = 0, 1
-TRACE_THREAD, TRACE_OCTET = 0, 1
+TRACE_THREAD, TRACE_OCTET, TRACE_PERSIST = 0, 1, 2
 
 
 class MpError(RuntimeError):
@@ -151,6 +151,8 @@ class MpRenderSettings(C.Structure):
         ("mode", C.c_uint32),
         ("order", C.c_uint32),
         ("tiles_per_batch", C.c_uint32),
+        ("trace_kernel", C.c_uint32),
+        ("_pad", C.c_uint32),
         ("seed", C.c_uint64),
     ]
 
@@ -185,6 +187,13 @@ PROTOTYPES = {
     "mp_device_count": (_i, [_P(_i)]),
     "mp_ctx_create": (_i, [_i, _P(_vp)]),
     "mp_ctx_destroy": (_i, [_vp]),
+    "mp_ctx_pool_acquire": (_i, [_i, _P(_vp)]),
+    "mp_ctx_pool_release": (_i, [_vp]),
+    "mp_ctx_pool_clear": (_i, []),
+    "mp_tiles_upload": (_i, [_vp, _P(MpTile), _u32, _u32]),
+    "mp_render_tile_range": (_i, [_vp, _u32, _u32, _P(MpRenderParams)]),
+    "mp_film_resolve_tiles_begin": (_i, [_vp, _u32, _u32, _u32, _u32, _i]),
+    "mp_film_resolve_tiles_end": (_i, [_vp, _i, _P(_vp)]),
     "mp_ctx_set_stream": (_i, [_vp, _vp]),
     "mp_ctx_set_trace_variant": (_i, [_vp, _u32]),
     "mp_ctx_sync": (_i, [_vp]),

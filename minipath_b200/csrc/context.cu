@@ -1,12 +1,15 @@
 // Device context and the C ABI around the kernels (include/minipath_b200.h).
 // nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -prec-div=true -prec-sqrt=true -lineinfo
+#include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "host_common.h"
 #include "kernels.cuh"
 #include "wavefront.cuh"
 #include "octet.cuh"
+#include "persist.cuh"
 #include "probes.cuh"
 
 using namespace mp;
@@ -30,9 +33,10 @@ struct MpCtx {
     void* d_scene_blob = nullptr;
     mpd::Scene scene{};
     mpd::SceneCM scene_cm{};
-    uint32_t trace_variant = MP_TRACE_OCTET;
+    uint32_t trace_variant = MP_TRACE_THREAD;
     int sm_count = 148;
     int octet_bps = 0;
+    int persist_bps = 0;
     size_t octet_bps_smem = 0;
     bool has_scene = false;
     uint32_t max_stack = 0;
@@ -46,6 +50,13 @@ struct MpCtx {
     uint32_t* d_rgba8 = nullptr;
     uint32_t* d_tile_out = nullptr;
     size_t tile_out_cap = 0;
+    struct TileSlot {  // double-buffered tile read-back of mp_film_resolve_tiles_begin / _end
+        uint32_t* d = nullptr;
+        uint8_t* h = nullptr;  // pinned
+        size_t cap = 0;
+        cudaEvent_t done = nullptr;
+    } slots[2];
+    size_t tiles_resident = 0;  // length of the list stored by mp_tiles_upload (0: d_tiles holds a staged batch)
     // counters
     mpd::DevCounters* d_counters = nullptr;
     // tile staging
@@ -82,6 +93,7 @@ static int stage_tiles(MpCtx* ctx, const MpTile* tiles, uint32_t n) {
         CK(cudaMallocHost(&ctx->h_tiles_pinned, cap * sizeof(MpTile)));
         ctx->tiles_cap = cap;
         ctx->tiles_staged = 0;
+        ctx->tiles_resident = 0;
     } else {
         // same tile list as the previous call (a frame re-rendered, the next sample pass): already on the device
         if (n == ctx->tiles_staged && memcmp(ctx->h_tiles_pinned, tiles, n * sizeof(MpTile)) == 0) return MP_OK;
@@ -89,14 +101,15 @@ static int stage_tiles(MpCtx* ctx, const MpTile* tiles, uint32_t n) {
         CK(cudaStreamSynchronize(ctx->stream));
     }
     ctx->tiles_staged = n;
+    ctx->tiles_resident = 0;
     memcpy(ctx->h_tiles_pinned, tiles, n * sizeof(MpTile));
     CK(cudaMemcpyAsync(ctx->d_tiles, ctx->h_tiles_pinned, n * sizeof(MpTile), cudaMemcpyHostToDevice, ctx->stream));
     return MP_OK;
 }
 
-static mpd::TileMap make_tile_map(MpCtx* ctx, uint32_t n_tiles, uint32_t tile_size) {
+static mpd::TileMap make_tile_map(MpCtx* ctx, uint32_t n_tiles, uint32_t tile_size, size_t first = 0) {
     mpd::TileMap tm;
-    tm.tiles = ctx->d_tiles;
+    tm.tiles = ctx->d_tiles + first;
     tm.n_tiles = n_tiles;
     tm.mt_x = (tile_size + 7) / 8;
     tm.threads_per_tile = tm.mt_x * ((tile_size + 3) / 4) * 32;
@@ -160,6 +173,11 @@ int mp_ctx_destroy(MpCtx* ctx) {
     if (ctx->film && ctx->film_owned) cudaFree(ctx->film);
     if (ctx->d_rgba8) cudaFree(ctx->d_rgba8);
     if (ctx->d_tile_out) cudaFree(ctx->d_tile_out);
+    for (auto& sl : ctx->slots) {
+        if (sl.d) cudaFree(sl.d);
+        if (sl.h) cudaFreeHost(sl.h);
+        if (sl.done) cudaEventDestroy(sl.done);
+    }
     if (ctx->d_counters) cudaFree(ctx->d_counters);
     if (ctx->d_tiles) cudaFree(ctx->d_tiles);
     if (ctx->h_tiles_pinned) cudaFreeHost(ctx->h_tiles_pinned);
@@ -167,6 +185,47 @@ int mp_ctx_destroy(MpCtx* ctx) {
     cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->own_stream);
     delete ctx;
+    return MP_OK;
+}
+
+// Process-wide pool of idle contexts, one list per device: mp_render() takes its workers' contexts from here so that
+// repeated renders reuse streams, films, path-state buffers and pinned staging instead of re-allocating them
+// (the reference keeps no such state, but its per-render cost is a thread spawn, not a 200 MB device allocation).
+static std::mutex g_pool_mutex;
+static std::vector<MpCtx*> g_pool;
+
+int mp_ctx_pool_acquire(int device, MpCtx** out) {
+    if (!out) return fail(MP_EINVAL, "null out");
+    {
+        std::lock_guard<std::mutex> g(g_pool_mutex);
+        for (size_t i = 0; i < g_pool.size(); ++i)
+            if (g_pool[i]->device == device) {
+                *out = g_pool[i];
+                g_pool.erase(g_pool.begin() + i);
+                return MP_OK;
+            }
+    }
+    return mp_ctx_create(device, out);
+}
+
+int mp_ctx_pool_release(MpCtx* ctx) {
+    if (!ctx) return MP_OK;
+    if (int rc = use_device(ctx)) return rc;
+    cudaStreamSynchronize(ctx->stream);
+    ctx->stream = ctx->own_stream;
+    ctx->count_visits = false;
+    std::lock_guard<std::mutex> g(g_pool_mutex);
+    g_pool.push_back(ctx);
+    return MP_OK;
+}
+
+int mp_ctx_pool_clear(void) {
+    std::vector<MpCtx*> all;
+    {
+        std::lock_guard<std::mutex> g(g_pool_mutex);
+        all.swap(g_pool);
+    }
+    for (MpCtx* c : all) mp_ctx_destroy(c);
     return MP_OK;
 }
 
@@ -179,7 +238,7 @@ int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream) {
 
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant) {
     if (!ctx) return fail(MP_EINVAL, "null context");
-    if (variant > MP_TRACE_OCTET) return fail(MP_EINVAL, "bad trace variant %u", variant);
+    if (variant > MP_TRACE_PERSIST) return fail(MP_EINVAL, "bad trace variant %u", variant);
     ctx->trace_variant = variant;
     return MP_OK;
 }
@@ -316,6 +375,7 @@ static int film_release(MpCtx* ctx) {
 int mp_film_create(MpCtx* ctx, uint32_t width, uint32_t height) {
     if (int rc = use_device(ctx)) return rc;
     if (width == 0 || height == 0 || (uint64_t)width * height > 0x7fffffffull) return fail(MP_EINVAL, "bad film size %ux%u", width, height);
+    if (ctx->film && ctx->film_owned && ctx->width == width && ctx->height == height) return mp_film_clear(ctx);  // pooled context: reuse
     if (int rc = film_release(ctx)) return rc;
     const size_t n = (size_t)width * height;
     CK(cudaMalloc(&ctx->film, n * sizeof(float4)));

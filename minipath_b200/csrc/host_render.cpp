@@ -31,6 +31,7 @@ struct MpRenderProgress {
     // RenderProgress (machinery.rs:125-129)
     size_t worker_count = 0;
     size_t batch = 1;
+    uint32_t trace_variant = MP_TRACE_THREAD;
     std::vector<std::thread> threads;
     std::atomic<size_t> threads_finished{0};
     MpStartedTileFn started = nullptr;
@@ -50,15 +51,49 @@ static void worker_fail(MpRenderProgress* p, int code) {
     p->next_tile_index.store(p->tile_ordering.size(), std::memory_order_release);  // stop the other workers too
 }
 
+// One batch in flight per read-back slot: rendered and resolved on the device, waiting to be copied into the image.
+struct Pending {
+    size_t first = 0, n = 0;
+    bool live = false;
+};
+
+// image.lock().copy_from(buffer.view(0,0,w,h), tile.min) (machinery.rs:78-89) + finished callbacks (:91-99)
+static int finish_batch(MpRenderProgress* p, MpCtx* ctx, Pending& b, int slot) {
+    if (!b.live) return MP_OK;
+    b.live = false;
+    const MpRenderSettings& s = p->settings;
+    const uint8_t* buffer = nullptr;
+    if (int rc = mp_film_resolve_tiles_end(ctx, slot, &buffer)) return rc;
+    const MpTile* tiles = &p->tile_ordering[b.first];
+    const size_t total = p->tile_ordering.size();
+    {
+        std::lock_guard<std::mutex> g(p->image_mutex);
+        for (size_t i = 0; i < b.n; ++i) {
+            const MpTile& t = tiles[i];
+            const size_t w = t.max_x - t.min_x;
+            for (uint32_t y = t.min_y; y < t.max_y; ++y)
+                memcpy(&p->image[((size_t)y * s.resolution_x + t.min_x) * 4], &buffer[((i * s.tile_size + (y - t.min_y)) * s.tile_size) * 4], w * 4);
+        }
+    }
+    if (p->finished) {
+        const size_t in_flight = p->worker_count * p->batch;
+        const size_t next_id = std::min(p->next_tile_index.load(std::memory_order_acquire), total + in_flight);
+        MpProgressSnapshot snap{next_id > in_flight ? std::min(next_id - in_flight, total) : 0, total};  // saturating_sub (machinery.rs:96)
+        for (size_t i = 0; i < b.n; ++i) p->finished(p->user, tiles[i], snap);
+    }
+    return MP_OK;
+}
+
 static void worker_main(MpRenderProgress* p, int device) {
     const MpRenderSettings& s = p->settings;
     const size_t total = p->tile_ordering.size();
     MpCtx* ctx = nullptr;
-    int rc = mp_ctx_create(device, &ctx);
+    int rc = mp_ctx_pool_acquire(device, &ctx);
+    if (!rc) rc = mp_ctx_set_trace_variant(ctx, p->trace_variant);
     if (!rc) rc = mp_scene_upload(ctx, p->scene);
     if (!rc) rc = mp_camera_set(ctx, &p->sampler);  // camera.build_sampler(settings.resolution) (machinery.rs:65)
     if (!rc) rc = mp_film_create(ctx, s.resolution_x, s.resolution_y);
-    std::vector<uint8_t> buffer(p->batch * (size_t)s.tile_size * s.tile_size * 4);  // tile buffers (machinery.rs:66-67)
+    if (!rc) rc = mp_tiles_upload(ctx, p->tile_ordering.data(), (uint32_t)total, s.tile_size);
     MpRenderParams params{};
     params.sample_count = s.sample_count;
     params.sample_base = 0;
@@ -69,37 +104,27 @@ static void worker_main(MpRenderProgress* p, int device) {
     params.seed = s.seed;
     if (rc) worker_fail(p, rc);
 
+    Pending pending[2];
+    int slot = 0;
     while (!rc) {
         const size_t first = p->next_tile_index.fetch_add(p->batch, std::memory_order_acq_rel);  // get_next_tile
         if (first >= total) break;
         const size_t n = std::min(p->batch, total - first);
-        const MpTile* tiles = &p->tile_ordering[first];
         if (p->started)
-            for (size_t i = 0; i < n; ++i) p->started(p->user, tiles[i]);
-        rc = mp_render_tiles(ctx, tiles, (uint32_t)n, &params);  // worker.render_tile (machinery.rs:77)
-        if (!rc) rc = mp_film_resolve_tiles_rgba8(ctx, tiles, (uint32_t)n, s.tile_size, s.sample_count, buffer.data());
-        if (rc) {
-            worker_fail(p, rc);
-            break;
-        }
-        {  // image.lock().copy_from(buffer.view(0,0,w,h), tile.min) (machinery.rs:78-89)
-            std::lock_guard<std::mutex> g(p->image_mutex);
-            for (size_t i = 0; i < n; ++i) {
-                const MpTile& t = tiles[i];
-                const size_t w = t.max_x - t.min_x;
-                for (uint32_t y = t.min_y; y < t.max_y; ++y)
-                    memcpy(&p->image[((size_t)y * s.resolution_x + t.min_x) * 4],
-                           &buffer[((i * s.tile_size + (y - t.min_y)) * s.tile_size) * 4], w * 4);
-            }
-        }
-        if (p->finished) {
-            const size_t next_id = std::min(p->next_tile_index.load(std::memory_order_acquire), total + p->worker_count * p->batch);
-            const size_t in_flight = p->worker_count * p->batch;
-            MpProgressSnapshot snap{next_id > in_flight ? std::min(next_id - in_flight, total) : 0, total};  // saturating_sub (machinery.rs:96)
-            for (size_t i = 0; i < n; ++i) p->finished(p->user, tiles[i], snap);
-        }
+            for (size_t i = 0; i < n; ++i) p->started(p->user, p->tile_ordering[first + i]);
+        rc = finish_batch(p, ctx, pending[slot], slot);  // this slot's previous batch (two batches back) leaves first
+        if (!rc) rc = mp_render_tile_range(ctx, (uint32_t)first, (uint32_t)n, &params);  // worker.render_tile (machinery.rs:77)
+        if (!rc) rc = mp_film_resolve_tiles_begin(ctx, (uint32_t)first, (uint32_t)n, s.tile_size, s.sample_count, slot);
+        if (rc) break;
+        pending[slot] = Pending{first, n, true};
+        slot ^= 1;
+        rc = finish_batch(p, ctx, pending[slot], slot);  // while this batch renders, the previous one goes into the image
     }
-    if (ctx) mp_ctx_destroy(ctx);
+    for (int k = 0; k < 2 && !rc; ++k) rc = finish_batch(p, ctx, pending[k ^ slot], k ^ slot);
+    if (rc) worker_fail(p, rc);
+    if (ctx) {
+        if (rc) mp_ctx_destroy(ctx); else mp_ctx_pool_release(ctx);
+    }
     {
         auto elapsed = std::chrono::steady_clock::now() - p->start_time;  // machinery.rs:107-113
         std::lock_guard<std::mutex> g(p->end_mutex);
@@ -119,6 +144,7 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
     if (!scene || !camera || !settings || !out) return fail(MP_EINVAL, "null argument");
     if (settings->tile_size == 0 || settings->sample_count == 0) return fail(MP_EINVAL, "tile_size and sample_count must be non-zero (NonZeroU32)");
     if (settings->resolution_x == 0 || settings->resolution_y == 0) return fail(MP_EINVAL, "empty resolution");
+    if (settings->trace_kernel > MP_TRACE_PERSIST + 1) return fail(MP_EINVAL, "bad trace_kernel");
     int have = 0;
     if (int rc = mp_device_count(&have)) return rc;
     if (have == 0) return fail(MP_ENODEVICE, "no CUDA device available; this library has no CPU fallback");
@@ -150,6 +176,11 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
                                   n_tiles, &n_tiles)) {
         delete p;
         return rc;
+    }
+    {  // traversal kernel: thread-per-ray unless the BVH needs a deeper stack than its local array holds
+        MpBvhStats st;
+        if (mp_bvh_stats(scene, &st) == MP_OK && st.max_stack > 128) p->trace_variant = MP_TRACE_OCTET;
+        if (settings->trace_kernel) p->trace_variant = settings->trace_kernel - 1;
     }
     p->worker_count = devs.size();
     // default batch: a quarter of each device's share, at least 32 tiles — big enough to fill 148 SMs for several waves,

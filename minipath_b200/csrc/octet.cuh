@@ -88,106 +88,149 @@ __device__ __forceinline__ OctetLane octet_lane() {
     return OctetLane{l & 7u, l & 24u, 0xFFu << (l & 24u)};
 }
 
-// One traversal step of one octet: pop the top entry and process it (inner node or leaf).  All 8 lanes hold identical
-// copies of (r, best, sp).  `stk` is the octet's shared-memory stack.  Returns with sp == 0 when the ray is finished.
-template <int ORDER, bool COUNT, bool NANPATH>
-__device__ __forceinline__ void octet_step(const Scene& sc, const SceneCM& cm, const OctetLane& ol, const Ray& r, bool any_hit,
-                                           uint2* __restrict__ stk, int& sp, Hit& best, Visits& vis) {
-    __syncwarp(ol.mask);  // entries written by sibling lanes in the previous step are visible
-    const uint2 e = stk[--sp];
-    if (__uint_as_float(e.y) > best.t) return;  // ray_bvh_intersection.rs:40
-    const uint32_t count = e.x & MP_LINK_COUNT_MASK, index = e.x >> MP_LINK_COUNT_BITS;
-    if (count == 0) {
-        // ---- inner node: lane k tests child k (ray_bvh_intersection.rs:149-162) ----
-        if (COUNT) vis.inner++;
-        const float4 b0 = __ldg(sc.inner_box + 2 * (size_t)index), b1 = __ldg(sc.inner_box + 2 * (size_t)index + 1);
-        const uint4 c = __ldg(cm.inner_cm + 8 * (size_t)index + ol.sub);
-        float t1;
-        bool hit = octet_child_slab<NANPATH>(c, f3(b0.x, b0.y, b0.z), f3(b1.x, b1.y, b1.z), r, best.t, t1);
-        hit = hit && c.w != MP_LINK_NULL;  // NULL children are discarded when popped (:49); skipping them is neutral
-        const uint32_t hits = (__ballot_sync(ol.mask, hit) >> ol.shift) & 0xFFu;
-        uint32_t pos;
-        if (ORDER == MP_ORDER_NEAR_FIRST) {
-            // far → near from the base; ties: lower lane nearer the top (same final order as the insertion in trace.cuh)
-            pos = 0;
-#pragma unroll
-            for (int k = 1; k < 8; ++k) {
-                const uint32_t j = (ol.sub + k) & 7u;
-                const float tj = __shfl_sync(ol.mask, t1, ol.shift + j);
-                if (((hits >> j) & 1u) && (tj > t1 || (tj == t1 && j > ol.sub))) ++pos;
-            }
-        } else {
-            pos = __popc(hits & ((1u << ol.sub) - 1u));  // lane order: lane 7 pops first (:161)
-        }
-        if (hit) stk[sp + pos] = make_uint2(c.w, __float_as_uint(t1));
-        sp += __popc(hits);
-    } else {
-        // ---- leaf: packets in order, lane k tests triangle k of each (ray_bvh_intersection.rs:104-141) ----
-        if (COUNT) vis.leaves++, vis.packets += count;
-        const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)index), b1 = __ldg(sc.packet_box + 2 * (size_t)index + 1);
-        const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
-        const float max_t = best.t;  // not updated inside the leaf
-        Hit local{MPD_INF, 0.0f, 0.0f, MP_NO_HIT};
-        for (uint32_t j = 0; j < count; ++j) {
-            const uint4* pk = cm.packets_cm + 9 * (size_t)(index + j);
-            const uint4 a = __ldg(pk + ol.sub);
-            const uint32_t zw = __ldg(reinterpret_cast<const uint32_t*>(pk + 8) + (ol.sub >> 1));
-            float t, u, v;
-            const bool valid = octet_tri(a, zw, ol.sub & 1u, bmin, bsize, r, max_t, t, u, v);
-            // first minimum over the 8 lanes in lane order (:127-135): min of t, then the lowest lane that attains it
-            const float key = valid ? t : MPD_INF;
-            float m = fminf(key, __shfl_xor_sync(ol.mask, key, 1));
-            m = fminf(m, __shfl_xor_sync(ol.mask, m, 2));
-            m = fminf(m, __shfl_xor_sync(ol.mask, m, 4));
-            const uint32_t eq = (__ballot_sync(ol.mask, valid && key == m) >> ol.shift) & 0xFFu;
-            if (eq) {  // uniform within the octet
-                const uint32_t win = __ffs(eq) - 1u;
-                const float tw = __shfl_sync(ol.mask, t, ol.shift + win);
-                const float uw = __shfl_sync(ol.mask, u, ol.shift + win);
-                const float vw = __shfl_sync(ol.mask, v, ol.shift + win);
-                if (tw < local.t) local = Hit{tw, uw, vw, (index + j) * 8u + win};
-            }
-        }
-        if (local.t < best.t) {  // :59
-            best = local;
-            if (any_hit) sp = 0;
-        }
-    }
-}
-
-// Drives one octet over rays i = first, first + stride, … < n.  fetch(i, r) loads ray i (all 8 lanes, identical values);
-// emit(i, best) is called by every lane of the octet when ray i is finished (lane sub == 0 should do the store).
-template <int ORDER, bool COUNT, class Fetch, class Emit>
+// Warp-synchronous driver.  The four octets of a warp run in lockstep through PHASES so that every ballot / shuffle is
+// a full-warp collective in converged code (a first version used octet-scoped masks: the compiler serialised each of
+// them per octet — VOTE executed with 8 of 32 threads — see profiles/r1_wf_trace_octet_v1_partialmask.txt):
+//   refill  an octet whose ray is finished emits the hit and loads its next ray (static stride over the queue)
+//   pop     every octet without pending work pops its stack until an entry survives `t1 > best.t` (:40)
+//   inner   octets holding an inner node test its 8 children, one per lane, and push the hits (:149-162)
+//   leaf    octets holding a leaf test ONE packet, one triangle per lane (:104-141); a leaf of c packets takes c phases
+// Per iteration the phase with more waiting octets runs; the others keep their pending entry.  Per ray the visiting
+// order, the `best.t` snapshots and the per-lane arithmetic are exactly those of trace.cuh.
+//
+// fetch(i, r) loads ray i into r.o, r.d (and r.inv unless INV_FROM_D) — identical values in all 8 lanes;
+// emit(i, best) is called by all 8 lanes when ray i is finished (lane sub == 0 stores).
+template <int ORDER, bool COUNT, bool INV_FROM_D, class Fetch, class Emit>
 __device__ __forceinline__ void octet_run(const Scene& sc, const SceneCM& cm, uint32_t n, uint32_t first, uint32_t stride, bool any_hit,
                                           uint2* __restrict__ stk, Fetch fetch, Emit emit, ThreadCounts& tc) {
+    constexpr uint32_t FULL = 0xffffffffu;
     const OctetLane ol = octet_lane();
     uint32_t cur = 0, next = first;
     bool have = false, nanpath = false;
     int sp = 0;
-    Ray r;
+    Ray r{};
     Hit best{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
+    bool pend_inner = false;  // an inner node popped and waiting for the inner phase
+    uint32_t p_index = 0;
+    uint32_t lf_index = 0, lf_rem = 0;  // leaf in progress: next packet, packets left
+    float lf_max_t = 0.0f;
+    Hit lf_local{MPD_INF, 0.0f, 0.0f, MP_NO_HIT};
+
     for (;;) {
-        if (sp == 0) {
-            if (have) {
-                emit(cur, best);
-                have = false;
+        // ---- refill ----
+        bool refilled = false;
+        if (have && !pend_inner && lf_rem == 0 && sp == 0) {
+            emit(cur, best);
+            have = false;
+        }
+        if (!have && next < n) {
+            cur = next, next += stride;
+            fetch(cur, r);
+            best = Hit{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
+            if (ol.sub == 0) stk[0] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
+            sp = 1;
+            have = refilled = true;
+            tc.rays++;
+        }
+        if (!__any_sync(FULL, have)) break;
+        if (__any_sync(FULL, refilled)) {
+            if (INV_FROM_D) {  // Ray::new's inv_direction (geometry/mod.rs:47), one division per lane instead of three
+                const uint32_t a = ol.sub % 3u;
+                const float dc = a == 0 ? r.d.x : (a == 1 ? r.d.y : r.d.z);
+                const float ic = dc == 0.0f ? MPD_INF : __fdiv_rn(1.0f, dc);
+                const float ix = __shfl_sync(FULL, ic, ol.shift + 0), iy = __shfl_sync(FULL, ic, ol.shift + 1), iz = __shfl_sync(FULL, ic, ol.shift + 2);
+                if (refilled) r.inv = f3(ix, iy, iz);
             }
-            if (next < n) {
-                cur = next, next += stride;
-                fetch(cur, r);
-                nanpath = (fabsf(r.inv.x) == MPD_INF) | (fabsf(r.inv.y) == MPD_INF) | (fabsf(r.inv.z) == MPD_INF);
-                best = Hit{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
-                if (ol.sub == 0) stk[0] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
-                sp = 1;
-                have = true;
-                tc.rays++;
+            if (refilled) nanpath = (fabsf(r.inv.x) == MPD_INF) | (fabsf(r.inv.y) == MPD_INF) | (fabsf(r.inv.z) == MPD_INF);
+        }
+        __syncwarp();  // stack entries written in the previous iteration (and the root just pushed) are visible
+
+        // ---- pop ----
+        bool need = have && !pend_inner && lf_rem == 0;
+        while (__any_sync(FULL, need)) {
+            if (need) {
+                if (sp == 0) {
+                    need = false;  // ray finished: emitted at the top of the next iteration
+                } else {
+                    const uint2 e = stk[--sp];
+                    if (!(__uint_as_float(e.y) > best.t)) {  // ray_bvh_intersection.rs:40
+                        need = false;
+                        const uint32_t count = e.x & MP_LINK_COUNT_MASK, index = e.x >> MP_LINK_COUNT_BITS;
+                        if (count == 0) {
+                            pend_inner = true, p_index = index;
+                        } else {
+                            lf_index = index, lf_rem = count, lf_max_t = best.t;  // max_t is not updated inside the leaf
+                            lf_local = Hit{MPD_INF, 0.0f, 0.0f, MP_NO_HIT};
+                            if (COUNT) tc.vis.leaves++, tc.vis.packets += count;
+                        }
+                    }
+                }
             }
         }
-        if (!have) break;  // this octet has no more rays; lanes of other octets keep going (octet-scoped sync only)
-        if (nanpath)
-            octet_step<ORDER, COUNT, true>(sc, cm, ol, r, any_hit, stk, sp, best, tc.vis);
-        else
-            octet_step<ORDER, COUNT, false>(sc, cm, ol, r, any_hit, stk, sp, best, tc.vis);
+
+        // ---- choose the phase ----
+        const uint32_t n_in = __popc(__ballot_sync(FULL, pend_inner)), n_lf = __popc(__ballot_sync(FULL, lf_rem != 0));
+        if (n_in != 0 && n_in >= n_lf) {
+            // ---- inner phase: lane k tests child k (ray_bvh_intersection.rs:149-162) ----
+            bool hit = false;
+            float t1 = 0.0f;
+            uint32_t link = MP_LINK_NULL;
+            if (pend_inner) {
+                if (COUNT) tc.vis.inner++;
+                const float4 b0 = __ldg(sc.inner_box + 2 * (size_t)p_index), b1 = __ldg(sc.inner_box + 2 * (size_t)p_index + 1);
+                const uint4 c = __ldg(cm.inner_cm + 8 * (size_t)p_index + ol.sub);
+                const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
+                hit = nanpath ? octet_child_slab<true>(c, bmin, bsize, r, best.t, t1) : octet_child_slab<false>(c, bmin, bsize, r, best.t, t1);
+                link = c.w;
+                hit = hit && link != MP_LINK_NULL;  // NULL children are discarded when popped (:49); skipping them is neutral
+            }
+            const uint32_t hits = (__ballot_sync(FULL, hit) >> ol.shift) & 0xFFu;
+            uint32_t pos;
+            if (ORDER == MP_ORDER_NEAR_FIRST) {
+                // far → near from the base; ties: lower lane nearer the top (same final order as the insertion in trace.cuh)
+                pos = 0;
+#pragma unroll
+                for (int k = 1; k < 8; ++k) {
+                    const uint32_t j = (ol.sub + k) & 7u;
+                    const float tj = __shfl_sync(FULL, t1, ol.shift + j);
+                    if (((hits >> j) & 1u) && (tj > t1 || (tj == t1 && j > ol.sub))) ++pos;
+                }
+            } else {
+                pos = __popc(hits & ((1u << ol.sub) - 1u));  // lane order: lane 7 pops first (:161)
+            }
+            if (hit) stk[sp + pos] = make_uint2(link, __float_as_uint(t1));
+            if (pend_inner) sp += __popc(hits);
+            pend_inner = false;
+        } else if (n_lf != 0) {
+            // ---- leaf phase: lane k tests triangle k of the leaf's next packet (ray_bvh_intersection.rs:104-141) ----
+            bool valid = false;
+            float t = 0.0f, u = 0.0f, v = 0.0f;
+            if (lf_rem != 0) {
+                const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)lf_index), b1 = __ldg(sc.packet_box + 2 * (size_t)lf_index + 1);
+                const uint4* pk = cm.packets_cm + 9 * (size_t)lf_index;
+                const uint4 a = __ldg(pk + ol.sub);
+                const uint32_t zw = __ldg(reinterpret_cast<const uint32_t*>(pk + 8) + (ol.sub >> 1));
+                valid = octet_tri(a, zw, ol.sub & 1u, f3(b0.x, b0.y, b0.z), f3(b1.x, b1.y, b1.z), r, lf_max_t, t, u, v);
+            }
+            // first minimum over the 8 lanes in lane order (:127-135): min of t, then the lowest lane that attains it
+            const float key = valid ? t : MPD_INF;
+            float m = fminf(key, __shfl_xor_sync(FULL, key, 1));
+            m = fminf(m, __shfl_xor_sync(FULL, m, 2));
+            m = fminf(m, __shfl_xor_sync(FULL, m, 4));
+            const uint32_t eq = (__ballot_sync(FULL, valid && key == m) >> ol.shift) & 0xFFu;
+            const uint32_t win = eq ? (uint32_t)__ffs(eq) - 1u : 0u;
+            const float tw = __shfl_sync(FULL, t, ol.shift + win);
+            const float uw = __shfl_sync(FULL, u, ol.shift + win);
+            const float vw = __shfl_sync(FULL, v, ol.shift + win);
+            if (lf_rem != 0) {
+                if (eq && tw < lf_local.t) lf_local = Hit{tw, uw, vw, lf_index * 8u + win};
+                ++lf_index;
+                if (--lf_rem == 0 && lf_local.t < best.t) {  // :59
+                    best = lf_local;
+                    if (any_hit) sp = 0;
+                }
+            }
+        }
     }
 }
 
@@ -201,16 +244,6 @@ __device__ __forceinline__ void octet_finish_counts(DevCounters* dc, ThreadCount
     flush_counts(dc, tc, count_visits);
 }
 
-// inv_direction as Ray::new computes it (geometry/mod.rs:47), one division per lane instead of three
-__device__ __forceinline__ void octet_inv(const OctetLane& ol, Ray& r) {
-    const uint32_t a = ol.sub % 3u;
-    const float dc = a == 0 ? r.d.x : (a == 1 ? r.d.y : r.d.z);
-    const float ic = dc == 0.0f ? MPD_INF : __fdiv_rn(1.0f, dc);
-    r.inv.x = __shfl_sync(ol.mask, ic, ol.shift + 0);
-    r.inv.y = __shfl_sync(ol.mask, ic, ol.shift + 1);
-    r.inv.z = __shfl_sync(ol.mask, ic, ol.shift + 2);
-}
-
 // Object::intersect on caller-provided rays (the bit-exactness gate), octet variant.
 template <int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) trace_rays_octet_kernel(Scene sc, SceneCM cm, const float* __restrict__ rays, uint32_t n,
@@ -218,7 +251,7 @@ __global__ void __launch_bounds__(128) trace_rays_octet_kernel(Scene sc, SceneCM
     extern __shared__ uint2 octet_stacks[];
     uint2* stk = octet_stacks + (threadIdx.x >> 3) * stack_cap;
     ThreadCounts tc{};
-    octet_run<ORDER, COUNT>(
+    octet_run<ORDER, COUNT, false>(
         sc, cm, n, blockIdx.x * OCTETS_PER_BLOCK + (threadIdx.x >> 3), gridDim.x * OCTETS_PER_BLOCK, false, stk,
         [&](uint32_t i, Ray& r) {
             const float* p = rays + 9 * (size_t)i;
@@ -244,13 +277,12 @@ __global__ void __launch_bounds__(128) wf_trace_octet_kernel(Scene sc, SceneCM c
     const OctetLane ol = octet_lane();
     ThreadCounts tc{};
     uint32_t path = 0;
-    octet_run<ORDER, COUNT>(
+    octet_run<ORDER, COUNT, true>(
         sc, cm, *count, blockIdx.x * OCTETS_PER_BLOCK + (threadIdx.x >> 3), gridDim.x * OCTETS_PER_BLOCK, false, stk,
         [&](uint32_t i, Ray& r) {
             path = queue[i];
             const float4 o = ray_o[path], d = ray_d[path];
             r.o = f3(o.x, o.y, o.z), r.d = f3(d.x, d.y, d.z);
-            octet_inv(ol, r);
         },
         [&](uint32_t, const Hit& h) {
             if (ol.sub == 0) hit[path] = make_uint4(h.tri, __float_as_uint(h.t), __float_as_uint(h.u), __float_as_uint(h.v));
@@ -269,12 +301,13 @@ __global__ void __launch_bounds__(128) wf_shadow_octet_kernel(Scene sc, SceneCM 
     const OctetLane ol = octet_lane();
     ThreadCounts tc{};
     float contribution = 0.0f;
-    octet_run<ORDER, COUNT>(
+    const Ray sun = ray_new(f3(0.f, 0.f, 0.f), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
+    octet_run<ORDER, COUNT, false>(
         sc, cm, *sh_count, blockIdx.x * OCTETS_PER_BLOCK + (threadIdx.x >> 3), gridDim.x * OCTETS_PER_BLOCK, true, stk,
         [&](uint32_t i, Ray& r) {
             const float4 o = sh_o[i];
             contribution = o.w;
-            r = ray_new(f3(o.x, o.y, o.z), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
+            r.o = f3(o.x, o.y, o.z), r.d = sun.d, r.inv = sun.inv;  // = ray_new(origin, sun): the direction is the same for all
             tc.shadow_rays++;
         },
         [&](uint32_t i, const Hit& h) {
