@@ -217,6 +217,8 @@ int mp_ctx_sync(MpCtx* ctx);
 #define MP_TRACE_OCTET 1u
 /* PERSIST = one thread per ray, persistent lanes that refill themselves, warp-voted inner / packet phases (persist.cuh) */
 #define MP_TRACE_PERSIST 2u
+/* HYBRID = THREAD for camera rays (coherent), PERSIST for bounce and shadow rays (incoherent) */
+#define MP_TRACE_HYBRID 3u
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant);
 /* Count traversal work (adds a few atomics per warp); off by default. */
 int mp_ctx_enable_counters(MpCtx* ctx, int on);

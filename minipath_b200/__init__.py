@@ -17,6 +17,7 @@ from ._ffi import (  # noqa: F401  (re-exported)
     NO_HIT,
     ORDER_NEAR_FIRST,
     ORDER_REFERENCE,
+    TRACE_HYBRID,
     TRACE_OCTET,
     TRACE_PERSIST,
     TRACE_THREAD,

@@ -31,6 +31,7 @@ struct MpCtx {
 
     // scene
     void* d_scene_blob = nullptr;
+    size_t scene_blob_cap = 0;
     mpd::Scene scene{};
     mpd::SceneCM scene_cm{};
     uint32_t trace_variant = MP_TRACE_THREAD;
@@ -238,7 +239,7 @@ int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream) {
 
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant) {
     if (!ctx) return fail(MP_EINVAL, "null context");
-    if (variant > MP_TRACE_PERSIST) return fail(MP_EINVAL, "bad trace variant %u", variant);
+    if (variant > MP_TRACE_HYBRID) return fail(MP_EINVAL, "bad trace variant %u", variant);
     ctx->trace_variant = variant;
     return MP_OK;
 }
@@ -292,15 +293,18 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     if (int rc = mp_bvh_stats(b, &st)) return rc;
     if (st.max_stack > MPD_OCTET_STACK_MAX) return fail(MP_EINVAL, "BVH depth %u needs a %u-entry stack (limit %d)", st.max_depth, st.max_stack, MPD_OCTET_STACK_MAX);
     CK(cudaStreamSynchronize(ctx->stream));
-    if (ctx->d_scene_blob) CK(cudaFree(ctx->d_scene_blob));
-    ctx->d_scene_blob = nullptr;
     // one allocation, every array 256-byte aligned
     auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
     const size_t s_inner = al((size_t)b->n_inner * sizeof(MpInnerNode)), s_ibox = al((size_t)b->n_inner * sizeof(MpBox));
     const size_t s_pack = al((size_t)b->n_packets * sizeof(MpTrianglePacket)), s_pbox = al((size_t)b->n_packets * sizeof(MpBox));
     const size_t s_sh = al((size_t)b->n_packets * 8 * sizeof(MpTriShading)), s_v = al((size_t)b->n_vertices * sizeof(MpVertexShading));
     const size_t total = 2 * s_inner + s_ibox + 2 * s_pack + s_pbox + s_sh + s_v + 256;
-    CK(cudaMalloc(&ctx->d_scene_blob, total));
+    if (total > ctx->scene_blob_cap) {  // pooled contexts keep the allocation between renders
+        if (ctx->d_scene_blob) CK(cudaFree(ctx->d_scene_blob));
+        ctx->d_scene_blob = nullptr, ctx->scene_blob_cap = 0, ctx->has_scene = false;
+        CK(cudaMalloc(&ctx->d_scene_blob, total));
+        ctx->scene_blob_cap = total;
+    }
     char* p = (char*)ctx->d_scene_blob;
     auto up = [&](const void* src, size_t bytes, size_t slot) -> const void* {
         const void* dst = p;

@@ -144,7 +144,7 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
     if (!scene || !camera || !settings || !out) return fail(MP_EINVAL, "null argument");
     if (settings->tile_size == 0 || settings->sample_count == 0) return fail(MP_EINVAL, "tile_size and sample_count must be non-zero (NonZeroU32)");
     if (settings->resolution_x == 0 || settings->resolution_y == 0) return fail(MP_EINVAL, "empty resolution");
-    if (settings->trace_kernel > MP_TRACE_PERSIST + 1) return fail(MP_EINVAL, "bad trace_kernel");
+    if (settings->trace_kernel > MP_TRACE_HYBRID + 1) return fail(MP_EINVAL, "bad trace_kernel");
     int have = 0;
     if (int rc = mp_device_count(&have)) return rc;
     if (have == 0) return fail(MP_ENODEVICE, "no CUDA device available; this library has no CPU fallback");
@@ -183,9 +183,11 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
         if (settings->trace_kernel) p->trace_variant = settings->trace_kernel - 1;
     }
     p->worker_count = devs.size();
-    // default batch: a quarter of each device's share, at least 32 tiles — big enough to fill 148 SMs for several waves,
-    // small enough that the dynamic queue still balances the tail and callbacks keep arriving
-    p->batch = settings->tiles_per_batch ? settings->tiles_per_batch : std::max<size_t>(32, n_tiles / (4 * devs.size()));
+    // default batch: one device takes the frame in one batch (every sample pass then runs at full width; small batches
+    // leave the late, thin bounce queues launch-bound); several devices take a quarter of their share at a time so the
+    // shared counter still balances the tail.  Callers that want tile callbacks to trickle in set tiles_per_batch.
+    p->batch = settings->tiles_per_batch ? settings->tiles_per_batch
+                                         : (devs.size() == 1 ? std::max<size_t>(1, n_tiles) : std::max<size_t>(32, n_tiles / (4 * devs.size())));
     p->started = started, p->finished = finished, p->user = user;
     p->start_time = std::chrono::steady_clock::now();
     try {
