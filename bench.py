@@ -47,7 +47,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="teapot-1080p", choices=sorted(WORKLOADS))
-    ap.add_argument("--mode", default="auto", choices=["auto", "megakernel", "wavefront-octet", "wavefront-thread", "wavefront-persist", "wavefront-hybrid"],
+    ap.add_argument("--mode", default="auto", choices=["auto", "megakernel", "wavefront-octet", "wavefront-thread", "wavefront-persist", "wavefront-hybrid", "wavefront-pool",
+                                                     "wavefront-hybrid-pool"],
                     help="megakernel: one thread per pixel; wavefront-*: staged kernels with the thread-per-ray, the 8-lanes-per-ray "
                          "(octet) or the persistent phased thread-per-ray traversal kernel")
     ap.add_argument("--order", default="reference", choices=["reference", "near_first"])
@@ -237,11 +238,13 @@ def run_b200(args, rank, local, world):
         dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
 
     modes = {"megakernel": mp.MODE_MEGAKERNEL, "wavefront-thread": mp.MODE_WAVEFRONT, "wavefront-octet": mp.MODE_WAVEFRONT,
-             "wavefront-persist": mp.MODE_WAVEFRONT, "wavefront-hybrid": mp.MODE_WAVEFRONT}
+             "wavefront-persist": mp.MODE_WAVEFRONT, "wavefront-hybrid": mp.MODE_WAVEFRONT,
+             "wavefront-pool": mp.MODE_WAVEFRONT, "wavefront-hybrid-pool": mp.MODE_WAVEFRONT}
     variants = {"megakernel": mp.TRACE_THREAD, "wavefront-thread": mp.TRACE_THREAD, "wavefront-octet": mp.TRACE_OCTET,
-                "wavefront-persist": mp.TRACE_PERSIST, "wavefront-hybrid": mp.TRACE_HYBRID}
+                "wavefront-persist": mp.TRACE_PERSIST, "wavefront-hybrid": mp.TRACE_HYBRID,
+                "wavefront-pool": mp.TRACE_POOL, "wavefront-hybrid-pool": mp.TRACE_HYBRID_POOL}
     if bvh.stats()["max_stack"] > 128:  # deeper than the local-memory stack of the thread-per-ray kernels
-        modes = {"wavefront-octet": mp.MODE_WAVEFRONT}
+        modes = {"wavefront-octet": mp.MODE_WAVEFRONT, "wavefront-pool": mp.MODE_WAVEFRONT}
 
     def make_step(mode_key):
         mode = modes[mode_key]
@@ -423,7 +426,9 @@ def roofline(args, res):
         "kernel": {"megakernel": "render_mega_kernel", "wavefront-octet": "wf_trace_octet_kernel+wf_shadow_octet_kernel",
                    "wavefront-thread": "wf_trace_kernel+wf_shadow_kernel",
                    "wavefront-persist": "wf_trace_persist_kernel+wf_shadow_persist_kernel",
-                   "wavefront-hybrid": "wf_trace_kernel (camera rays) + wf_trace_persist_kernel+wf_shadow_persist_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
+                   "wavefront-hybrid": "wf_trace_kernel (camera rays) + wf_trace_persist_kernel+wf_shadow_persist_kernel",
+                   "wavefront-pool": "wf_trace_pool_kernel+wf_shadow_pool_kernel",
+                   "wavefront-hybrid-pool": "wf_trace_kernel (camera rays) + wf_trace_pool_kernel+wf_shadow_pool_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
         "peak_source": "FP32 FMA and L2 read bandwidth measured by mp_probe_* in this run; HBM " + hbm_src,
         "fp32": {"achieved_tflops": flops / secs / 1e12, "peak_tflops": fp32, "frac": t_fp32 / secs},
         "l2": {"achieved_gbs": bytes_ / secs / 1e9, "peak_gbs": l2, "frac": t_l2 / secs},

@@ -219,6 +219,10 @@ int mp_ctx_sync(MpCtx* ctx);
 #define MP_TRACE_PERSIST 2u
 /* HYBRID = THREAD for camera rays (coherent), PERSIST for bounce and shadow rays (incoherent) */
 #define MP_TRACE_HYBRID 3u
+/* POOL = each warp owns a pool of 96 rays (state in shared memory, stacks in a global scratch) and runs 32 work items of ONE
+ * kind (inner node / triangle packet) in lockstep per round (pool.cuh); HYBRID_POOL = THREAD for camera rays, POOL after */
+#define MP_TRACE_POOL 4u
+#define MP_TRACE_HYBRID_POOL 5u
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant);
 /* Count traversal work (adds a few atomics per warp); off by default. */
 int mp_ctx_enable_counters(MpCtx* ctx, int on);

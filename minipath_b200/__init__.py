@@ -18,6 +18,8 @@ from ._ffi import (  # noqa: F401  (re-exported)
     ORDER_NEAR_FIRST,
     ORDER_REFERENCE,
     TRACE_HYBRID,
+    TRACE_HYBRID_POOL,
+    TRACE_POOL,
     TRACE_OCTET,
     TRACE_PERSIST,
     TRACE_THREAD,

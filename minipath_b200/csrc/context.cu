@@ -10,6 +10,7 @@
 #include "wavefront.cuh"
 #include "octet.cuh"
 #include "persist.cuh"
+#include "pool.cuh"
 #include "probes.cuh"
 
 using namespace mp;
@@ -38,6 +39,10 @@ struct MpCtx {
     int sm_count = 148;
     int octet_bps = 0;
     int persist_bps = 0;
+    int pool_bps = 0;
+    uint2* pool_scratch = nullptr;
+    size_t pool_scratch_cap = 0;
+    uint32_t* d_claim = nullptr;
     size_t octet_bps_smem = 0;
     bool has_scene = false;
     uint32_t max_stack = 0;
@@ -174,6 +179,8 @@ int mp_ctx_destroy(MpCtx* ctx) {
     if (ctx->film && ctx->film_owned) cudaFree(ctx->film);
     if (ctx->d_rgba8) cudaFree(ctx->d_rgba8);
     if (ctx->d_tile_out) cudaFree(ctx->d_tile_out);
+    if (ctx->pool_scratch) cudaFree(ctx->pool_scratch);
+    if (ctx->d_claim) cudaFree(ctx->d_claim);
     for (auto& sl : ctx->slots) {
         if (sl.d) cudaFree(sl.d);
         if (sl.h) cudaFreeHost(sl.h);
@@ -239,7 +246,7 @@ int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream) {
 
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant) {
     if (!ctx) return fail(MP_EINVAL, "null context");
-    if (variant > MP_TRACE_HYBRID) return fail(MP_EINVAL, "bad trace variant %u", variant);
+    if (variant > MP_TRACE_HYBRID_POOL) return fail(MP_EINVAL, "bad trace variant %u", variant);
     ctx->trace_variant = variant;
     return MP_OK;
 }

@@ -1,0 +1,274 @@
+// BVH8 traversal with a per-warp RAY POOL — the fifth traversal variant (MP_TRACE_POOL).
+//
+// The thread-per-ray kernels lose most of the machine to SIMT divergence on incoherent rays: at any moment some lanes want
+// an inner node (8 slab tests), some a triangle packet (8 Möller–Trumbore tests), some are finished (profiles/r1_wf_trace_thread.txt:
+// 7-11 of 32 threads active on bounce rays).  Here a warp does not own 32 rays but a POOL of 96, whose state lives in shared
+// memory (ray, best hit, leaf-in-progress; SoA, 4-byte columns) with the stacks in a global scratch area.  Every ray has exactly
+// one pending work item — an inner node or ONE packet of a leaf — and the warp keeps three small ring queues of slot ids
+// (inner items, packet items, free slots).  Each round the warp takes 32 items OF ONE KIND and runs them in lockstep, so all 32
+// lanes execute the same code on real work; then every lane pops its ray's next surviving stack entry (`t1 > best.t`,
+// ray_bvh_intersection.rs:40) and files the slot under the right queue, or emits the hit and frees the slot.  With 64..96 rays
+// alive, one of the two queues always holds at least 32 items; free slots are refilled 32 at a time with consecutive rays of the
+// input queue (claimed with one atomicAdd), which also keeps the ray fetch coalesced.
+//
+// Per ray, the visiting order, the `best.t` snapshots (max_t at node pop, leaf-local best, :106-107,:59) and the arithmetic are
+// exactly those of trace.cuh, hence the same bits.
+#pragma once
+#include "persist.cuh"
+
+namespace mpd {
+
+#define POOL_W 96       // ray slots per warp
+#define POOL_RING 128   // ring capacity (power of two >= POOL_W)
+#define POOL_COLS 22    // 4-byte state columns per slot
+#define POOL_WARPS 4    // warps per block
+#define POOL_SMEM_PER_WARP (POOL_COLS * POOL_W * 4 + 3 * POOL_RING)
+
+struct PoolWarp {  // shared-memory view of one warp's pool
+    float* col;          // [POOL_COLS][POOL_W]
+    unsigned char* ring; // [3][POOL_RING]: 0 inner items, 1 packet items, 2 free slots
+    __device__ __forceinline__ float& f(int c, uint32_t s) const { return col[c * POOL_W + s]; }
+    __device__ __forceinline__ uint32_t& u(int c, uint32_t s) const { return reinterpret_cast<uint32_t*>(col)[c * POOL_W + s]; }
+};
+// columns
+enum { PC_OX, PC_OY, PC_OZ, PC_DX, PC_DY, PC_DZ, PC_IX, PC_IY, PC_IZ, PC_BT, PC_BU, PC_BV, PC_BTRI, PC_SP, PC_RID, PC_PIDX, PC_REM,
+       PC_LMAX, PC_LT, PC_LU, PC_LV, PC_LTRI };
+
+struct PoolQueues {  // warp-uniform ring cursors
+    uint32_t head[3], tail[3];
+    __device__ __forceinline__ uint32_t size(int q) const { return tail[q] - head[q]; }
+};
+
+// All 32 lanes call this; lanes with pred append their slot to ring q.
+__device__ __forceinline__ void pool_push(const PoolWarp& pw, PoolQueues& qs, int q, bool pred, uint32_t slot) {
+    const uint32_t m = __ballot_sync(0xffffffffu, pred);
+    if (pred) pw.ring[q * POOL_RING + ((qs.tail[q] + __popc(m & ((1u << (threadIdx.x & 31u)) - 1u))) & (POOL_RING - 1))] = (unsigned char)slot;
+    qs.tail[q] += __popc(m);
+}
+
+// Pop the ray's next surviving entry and file the slot; `active` lanes own `slot` with current (sp, best_t).
+template <bool COUNT, class Emit>
+__device__ __forceinline__ void pool_advance(const PoolWarp& pw, PoolQueues& qs, bool active, uint32_t slot, uint2* stk, int sp, float best_t,
+                                             Emit emit, ThreadCounts& tc) {
+    uint32_t kind = 0;  // 0 finished, 1 inner, 2 leaf
+    if (active) {
+        while (sp > 0) {
+            const uint2 e = stk[--sp];
+            if (__uint_as_float(e.y) > best_t) continue;  // ray_bvh_intersection.rs:40
+            const uint32_t count = e.x & MP_LINK_COUNT_MASK;
+            pw.u(PC_PIDX, slot) = e.x >> MP_LINK_COUNT_BITS;
+            pw.u(PC_REM, slot) = count;
+            if (count == 0) {
+                kind = 1;
+            } else {
+                kind = 2;
+                pw.f(PC_LMAX, slot) = best_t;  // max_t is not updated inside the leaf
+                pw.f(PC_LT, slot) = MPD_INF;
+                pw.u(PC_LTRI, slot) = MP_NO_HIT;
+                if (COUNT) tc.vis.leaves++, tc.vis.packets += count;
+            }
+            break;
+        }
+        pw.u(PC_SP, slot) = (uint32_t)sp;
+        if (kind == 0)
+            emit(pw.u(PC_RID, slot), Hit{pw.f(PC_BT, slot), pw.f(PC_BU, slot), pw.f(PC_BV, slot), pw.u(PC_BTRI, slot)});
+    }
+    pool_push(pw, qs, 0, active && kind == 1, slot);
+    pool_push(pw, qs, 1, active && kind == 2, slot);
+    pool_push(pw, qs, 2, active && kind == 0, slot);
+}
+
+__device__ __forceinline__ Ray pool_load_ray(const PoolWarp& pw, uint32_t s) {
+    Ray r;
+    r.o = f3(pw.f(PC_OX, s), pw.f(PC_OY, s), pw.f(PC_OZ, s));
+    r.d = f3(pw.f(PC_DX, s), pw.f(PC_DY, s), pw.f(PC_DZ, s));
+    r.inv = f3(pw.f(PC_IX, s), pw.f(PC_IY, s), pw.f(PC_IZ, s));
+    return r;
+}
+
+// fetch(i, r) loads ray i completely (o, d, inv); emit(i, hit) stores its result.  `claim` is a zeroed device counter shared by
+// the launch: warps claim 32 consecutive rays at a time.  `scratch` holds gridDim.x * POOL_WARPS * POOL_W stacks of stack_cap entries.
+template <int ORDER, bool COUNT, class Fetch, class Emit>
+__device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* claim, bool any_hit, uint2* __restrict__ scratch, uint32_t stack_cap,
+                                         unsigned char* smem, Fetch fetch, Emit emit, ThreadCounts& tc) {
+    constexpr uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    PoolWarp pw;
+    pw.col = reinterpret_cast<float*>(smem + (size_t)warp * POOL_SMEM_PER_WARP);
+    pw.ring = smem + (size_t)warp * POOL_SMEM_PER_WARP + POOL_COLS * POOL_W * 4;
+    uint2* const wstacks = scratch + ((size_t)blockIdx.x * POOL_WARPS + warp) * POOL_W * stack_cap;
+    PoolQueues qs{};
+    for (uint32_t s = lane; s < POOL_W; s += 32) pw.ring[2 * POOL_RING + s] = (unsigned char)s;  // every slot starts free
+    qs.tail[2] = POOL_W;
+    bool more = true;  // the input queue may still hold rays
+    __syncwarp();
+
+    for (;;) {
+        const uint32_t n_in = qs.size(0), n_lf = qs.size(1), n_free = qs.size(2);
+        // ---- refill: 32 free slots (or the pool is nearly empty) and rays left ----
+        if (more && (n_free >= 32 || (n_in < 32 && n_lf < 32 && n_free > 0))) {
+            const uint32_t want = n_free < 32 ? n_free : 32;
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(claim, want);
+            base = __shfl_sync(FULL, base, 0);
+            const uint32_t got = base >= n ? 0 : (n - base < want ? n - base : want);
+            if (got < want) more = false;
+            const bool act = lane < got;
+            uint32_t slot = 0;
+            if (act) {
+                slot = pw.ring[2 * POOL_RING + ((qs.head[2] + lane) & (POOL_RING - 1))];
+                Ray r;
+                fetch(base + lane, r);
+                pw.f(PC_OX, slot) = r.o.x, pw.f(PC_OY, slot) = r.o.y, pw.f(PC_OZ, slot) = r.o.z;
+                pw.f(PC_DX, slot) = r.d.x, pw.f(PC_DY, slot) = r.d.y, pw.f(PC_DZ, slot) = r.d.z;
+                pw.f(PC_IX, slot) = r.inv.x, pw.f(PC_IY, slot) = r.inv.y, pw.f(PC_IZ, slot) = r.inv.z;
+                pw.f(PC_BT, slot) = MPD_FLT_MAX, pw.f(PC_BU, slot) = 0.0f, pw.f(PC_BV, slot) = 0.0f, pw.u(PC_BTRI, slot) = MP_NO_HIT;
+                pw.u(PC_RID, slot) = base + lane;
+                wstacks[(size_t)slot * stack_cap] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
+                tc.rays++;
+            }
+            qs.head[2] += got;
+            pool_advance<COUNT>(pw, qs, act, slot, wstacks + (size_t)slot * stack_cap, 1, MPD_FLT_MAX, emit, tc);
+            __syncwarp();
+            continue;
+        }
+        if (n_in == 0 && n_lf == 0) break;  // nothing pending and nothing left to fetch
+
+        if (n_in >= n_lf) {
+            // ---- 32 inner nodes (ray_bvh_intersection.rs:149-162) ----
+            const uint32_t take = n_in < 32 ? n_in : 32;
+            const bool act = lane < take;
+            uint32_t slot = 0;
+            int sp = 0;
+            float bt = 0.0f;
+            uint2* stk = wstacks;
+            if (act) {
+                slot = pw.ring[0 * POOL_RING + ((qs.head[0] + lane) & (POOL_RING - 1))];
+                stk = wstacks + (size_t)slot * stack_cap;
+                const Ray r = pool_load_ray(pw, slot);
+                bt = pw.f(PC_BT, slot);
+                sp = (int)pw.u(PC_SP, slot);
+                const uint32_t node = pw.u(PC_PIDX, slot);
+                if (COUNT) tc.vis.inner++;
+                const bool nanpath = (fabsf(r.inv.x) == MPD_INF) | (fabsf(r.inv.y) == MPD_INF) | (fabsf(r.inv.z) == MPD_INF);
+                if (nanpath)
+                    persist_inner<true>(sc, r, node, bt, stk, sp, ORDER);
+                else
+                    persist_inner<false>(sc, r, node, bt, stk, sp, ORDER);
+            }
+            qs.head[0] += take;
+            pool_advance<COUNT>(pw, qs, act, slot, stk, sp, bt, emit, tc);
+        } else {
+            // ---- 32 triangle packets, one per ray (ray_bvh_intersection.rs:104-141) ----
+            const uint32_t take = n_lf < 32 ? n_lf : 32;
+            const bool act = lane < take;
+            uint32_t slot = 0;
+            int sp = 0;
+            float bt = 0.0f;
+            uint2* stk = wstacks;
+            bool done = false;  // the leaf's last packet has been tested
+            if (act) {
+                slot = pw.ring[1 * POOL_RING + ((qs.head[1] + lane) & (POOL_RING - 1))];
+                stk = wstacks + (size_t)slot * stack_cap;
+                const Ray r = pool_load_ray(pw, slot);
+                uint32_t pidx = pw.u(PC_PIDX, slot), rem = pw.u(PC_REM, slot);
+                const float max_t = pw.f(PC_LMAX, slot);
+                Hit local{pw.f(PC_LT, slot), pw.f(PC_LU, slot), pw.f(PC_LV, slot), pw.u(PC_LTRI, slot)};
+                const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)pidx), b1 = __ldg(sc.packet_box + 2 * (size_t)pidx + 1);
+                const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
+                const uint4* pk = sc.packets + 9 * (size_t)pidx;
+                uint4 q[9];
+#pragma unroll
+                for (int k = 0; k < 9; ++k) q[k] = __ldg(pk + k);
+#pragma unroll
+                for (int tl = 0; tl < 8; ++tl) {
+                    float t, u, v;
+                    if (tri_lane(q, tl, bmin, bsize, r, max_t, t, u, v) && t < local.t) {
+                        local.t = t, local.u = u, local.v = v;
+                        local.tri = pidx * 8u + (uint32_t)tl;
+                    }
+                }
+                ++pidx, --rem;
+                pw.u(PC_PIDX, slot) = pidx, pw.u(PC_REM, slot) = rem;
+                sp = (int)pw.u(PC_SP, slot);
+                bt = pw.f(PC_BT, slot);
+                if (rem == 0) {
+                    done = true;
+                    if (local.t < bt) {  // :59
+                        bt = local.t;
+                        pw.f(PC_BT, slot) = local.t, pw.f(PC_BU, slot) = local.u, pw.f(PC_BV, slot) = local.v, pw.u(PC_BTRI, slot) = local.tri;
+                        if (any_hit) sp = 0;
+                    }
+                } else {
+                    pw.f(PC_LT, slot) = local.t, pw.f(PC_LU, slot) = local.u, pw.f(PC_LV, slot) = local.v, pw.u(PC_LTRI, slot) = local.tri;
+                }
+            }
+            qs.head[1] += take;
+            pool_push(pw, qs, 1, act && !done, slot);  // more packets of the same leaf: back into the packet queue
+            pool_advance<COUNT>(pw, qs, act && done, slot, stk, sp, bt, emit, tc);
+        }
+        __syncwarp();
+    }
+}
+
+// ---- kernels: 128 threads = 4 pools per block, persistent grid ----
+
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) trace_rays_pool_kernel(Scene sc, const float* __restrict__ rays, uint32_t n, uint4* __restrict__ hits,
+                                                              DevCounters* dc, uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
+    extern __shared__ __align__(16) unsigned char pool_smem[];
+    ThreadCounts tc{};
+    pool_run<ORDER, COUNT>(
+        sc, n, claim, false, scratch, stack_cap, pool_smem,
+        [&](uint32_t i, Ray& r) {
+            const float* p = rays + 9 * (size_t)i;
+            r.o = f3(__ldg(p + 0), __ldg(p + 1), __ldg(p + 2));
+            r.d = f3(__ldg(p + 3), __ldg(p + 4), __ldg(p + 5));
+            r.inv = f3(__ldg(p + 6), __ldg(p + 7), __ldg(p + 8));
+        },
+        [&](uint32_t i, const Hit& h) { hits[i] = make_uint4(h.tri, __float_as_uint(h.t), __float_as_uint(h.u), __float_as_uint(h.v)); }, tc);
+    flush_counts(dc, tc, COUNT);
+}
+
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) wf_trace_pool_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
+                                                            const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
+                                                            uint4* __restrict__ hit, DevCounters* dc, uint32_t* claim, uint2* scratch,
+                                                            uint32_t stack_cap) {
+    extern __shared__ __align__(16) unsigned char pool_smem[];
+    ThreadCounts tc{};
+    pool_run<ORDER, COUNT>(
+        sc, *count, claim, false, scratch, stack_cap, pool_smem,
+        [&](uint32_t i, Ray& r) {
+            const uint32_t path = queue[i];
+            r = load_ray(ray_o[path], ray_d[path]);
+        },
+        [&](uint32_t i, const Hit& h) { hit[queue[i]] = make_uint4(h.tri, __float_as_uint(h.t), __float_as_uint(h.u), __float_as_uint(h.v)); }, tc);
+    flush_counts(dc, tc, COUNT);
+}
+
+template <int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) wf_shadow_pool_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
+                                                             const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, DevCounters* dc,
+                                                             uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
+    extern __shared__ __align__(16) unsigned char pool_smem[];
+    ThreadCounts tc{};
+    const Ray sun = ray_new(f3(0.f, 0.f, 0.f), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
+    pool_run<ORDER, COUNT>(
+        sc, *sh_count, claim, true, scratch, stack_cap, pool_smem,
+        [&](uint32_t i, Ray& r) {
+            const float4 o = sh_o[i];
+            r.o = f3(o.x, o.y, o.z), r.d = sun.d, r.inv = sun.inv;  // = ray_new(origin, sun)
+            tc.shadow_rays++;
+        },
+        [&](uint32_t i, const Hit& h) {
+            if (h.tri == MP_NO_HIT) {
+                const uint32_t path = sh_path[i];
+                ray_d[path].w = __fadd_rn(ray_d[path].w, sh_o[i].w);
+            }
+        },
+        tc);
+    flush_counts(dc, tc, COUNT);
+}
+
+}  // namespace mpd

@@ -19,7 +19,7 @@ struct WavefrontBuffers {
     uint32_t* queue[2] = {nullptr, nullptr};
     float4* sh_o = nullptr;       // shadow ray origin.xyz, contribution
     uint32_t* sh_path = nullptr;
-    uint32_t* counts = nullptr;   // [0 .. WF_MAX_DEPTH+1] queue sizes per depth, then [.. 2*(WF_MAX_DEPTH+1)] shadow queue sizes
+    uint32_t* counts = nullptr;   // 4 rows of WF_MAX_DEPTH+2: queue sizes per depth, shadow queue sizes, pool claim cursors (trace), (shadow)
 };
 
 inline void wavefront_free(WavefrontBuffers& w) {
@@ -42,7 +42,7 @@ inline cudaError_t wavefront_reserve(WavefrontBuffers& w, size_t cap) {
     WF_ALLOC(w.queue[1], cap * sizeof(uint32_t))
     WF_ALLOC(w.sh_o, cap * sizeof(float4))
     WF_ALLOC(w.sh_path, cap * sizeof(uint32_t))
-    WF_ALLOC(w.counts, 2 * (WF_MAX_DEPTH + 2) * sizeof(uint32_t))
+    WF_ALLOC(w.counts, 4 * (WF_MAX_DEPTH + 2) * sizeof(uint32_t))
 #undef WF_ALLOC
     w.cap = cap;
     return cudaSuccess;
