@@ -52,6 +52,8 @@ def parse_args():
                     help="megakernel: one thread per pixel; wavefront-*: staged kernels with the thread-per-ray, the 8-lanes-per-ray "
                          "(octet) or the persistent phased thread-per-ray traversal kernel")
     ap.add_argument("--order", default="reference", choices=["reference", "near_first"])
+    ap.add_argument("--layout", default="decoded", choices=["decoded", "quantised"],
+                    help="node layout read by the traversal kernels: f32 boxes/edges decoded at upload (default) or the reference's u16 records")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel")
     ap.add_argument("--bounces", type=int, default=-1, help="override the workload's max_bounces")
     ap.add_argument("--shard", default="spp", choices=["spp", "tiles"])
@@ -227,6 +229,7 @@ def run_b200(args, rank, local, world):
     stream = torch.cuda.Stream()
     ctx = mp.Context(local)
     ctx.set_stream(stream.cuda_stream)
+    ctx.set_node_layout(mp.LAYOUT_DECODED if args.layout == "decoded" else mp.LAYOUT_QUANTISED)
     ctx.upload_scene(bvh)
     ctx.set_camera(sampler)
     film = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
@@ -466,7 +469,7 @@ def main():
                                                                          "a procedural Sponza STAND-IN (sponza.obj is absent from the reference)"),
             "samples_per_s": res["samples_per_s"],
             "config": {"workload": args.workload, "resolution": [w, h], "spp_per_gpu": spp, "spp_total": spp * world if args.shard == "spp" else spp,
-                       "max_bounces": bounces, "tile_size": 64, "pipeline": res["mode_name"], "traversal_order": args.order,
+                       "max_bounces": bounces, "tile_size": 64, "pipeline": res["mode_name"], "traversal_order": args.order, "node_layout": args.layout,
                        "pipeline_ab_ms": res["ab"], "sharding": args.shard if world > 1 else "none",
                        "bvh": {"triangles": st["n_triangles"], "inner_nodes": st["n_inner"], "packets": st["n_packets"]},
                        "l2": "flushed between timed steps (256 MB fill outside the event pairs)",

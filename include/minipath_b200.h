@@ -224,6 +224,15 @@ int mp_ctx_sync(MpCtx* ctx);
 #define MP_TRACE_POOL 4u
 #define MP_TRACE_HYBRID_POOL 5u
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant);
+/* Node layout the THREAD / PERSIST / POOL kernels and the megakernel read (same results, bit for bit):
+ * QUANTISED = the reference records as they are (InnerNode 128 B, RelativeTriangle8 144 B; u16 → f32 on every visit,
+ *             compressed_geometry.rs:95-110,160-162);
+ * DECODED   = the dequantisation hoisted to upload time: f32 child boxes (256 B per node) and f32 v0 / e1 / e2 per triangle
+ *             (288 B per packet), written once by a device kernel with the same fma — default, ~2x fewer instructions per visit.
+ * Takes effect at the next mp_scene_upload only for the memory it allocates; switching is allowed at any time. */
+#define MP_LAYOUT_QUANTISED 0u
+#define MP_LAYOUT_DECODED 1u
+int mp_ctx_set_node_layout(MpCtx* ctx, uint32_t layout);
 /* Count traversal work (adds a few atomics per warp); off by default. */
 int mp_ctx_enable_counters(MpCtx* ctx, int on);
 int mp_counters(MpCtx* ctx, MpCounters* out);

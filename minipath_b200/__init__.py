@@ -12,6 +12,8 @@ import numpy as np
 
 from . import _ffi
 from ._ffi import (  # noqa: F401  (re-exported)
+    LAYOUT_DECODED,
+    LAYOUT_QUANTISED,
     MODE_MEGAKERNEL,
     MODE_WAVEFRONT,
     NO_HIT,
@@ -405,6 +407,10 @@ class Context:
 
     def set_trace_variant(self, variant):
         check(lib.mp_ctx_set_trace_variant(self._h, variant))
+
+    def set_node_layout(self, layout):
+        """LAYOUT_DECODED (default: f32 child boxes / triangle edges written at upload) or LAYOUT_QUANTISED (reference records)."""
+        check(lib.mp_ctx_set_node_layout(self._h, layout))
 
     def sync(self):
         check(lib.mp_ctx_sync(self._h))

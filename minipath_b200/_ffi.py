@@ -19,6 +19,7 @@ TRI_FLAT = 0x80000000
 MODE_MEGAKERNEL, MODE_WAVEFRONT = 0, 1
 ORDER_REFERENCE, ORDER_NEAR_FIRST = 0, 1
 TRACE_THREAD, TRACE_OCTET, TRACE_PERSIST, TRACE_HYBRID, TRACE_POOL, TRACE_HYBRID_POOL = 0, 1, 2, 3, 4, 5
+LAYOUT_QUANTISED, LAYOUT_DECODED = 0, 1
 
 
 class MpError(RuntimeError):
@@ -196,6 +197,7 @@ PROTOTYPES = {
     "mp_film_resolve_tiles_end": (_i, [_vp, _i, _P(_vp)]),
     "mp_ctx_set_stream": (_i, [_vp, _vp]),
     "mp_ctx_set_trace_variant": (_i, [_vp, _u32]),
+    "mp_ctx_set_node_layout": (_i, [_vp, _u32]),
     "mp_ctx_sync": (_i, [_vp]),
     "mp_ctx_enable_counters": (_i, [_vp, _i]),
     "mp_counters": (_i, [_vp, _P(MpCounters)]),

@@ -11,6 +11,7 @@
 #include "octet.cuh"
 #include "persist.cuh"
 #include "pool.cuh"
+#include "decode.cuh"
 #include "probes.cuh"
 
 using namespace mp;
@@ -36,6 +37,9 @@ struct MpCtx {
     mpd::Scene scene{};
     mpd::SceneCM scene_cm{};
     uint32_t trace_variant = MP_TRACE_THREAD;
+    uint32_t layout = MP_LAYOUT_DECODED;  // requested node layout
+    bool decoded_ok = false;              // the decoded arrays exist and passed the min <= max check
+    uint32_t* d_flags = nullptr;
     int sm_count = 148;
     int octet_bps = 0;
     int persist_bps = 0;
@@ -181,6 +185,7 @@ int mp_ctx_destroy(MpCtx* ctx) {
     if (ctx->d_tile_out) cudaFree(ctx->d_tile_out);
     if (ctx->pool_scratch) cudaFree(ctx->pool_scratch);
     if (ctx->d_claim) cudaFree(ctx->d_claim);
+    if (ctx->d_flags) cudaFree(ctx->d_flags);
     for (auto& sl : ctx->slots) {
         if (sl.d) cudaFree(sl.d);
         if (sl.h) cudaFreeHost(sl.h);
@@ -251,6 +256,13 @@ int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant) {
     return MP_OK;
 }
 
+int mp_ctx_set_node_layout(MpCtx* ctx, uint32_t layout) {
+    if (!ctx) return fail(MP_EINVAL, "null context");
+    if (layout > MP_LAYOUT_DECODED) return fail(MP_EINVAL, "bad node layout %u", layout);
+    ctx->layout = layout;
+    return MP_OK;
+}
+
 int mp_ctx_sync(MpCtx* ctx) {
     if (int rc = use_device(ctx)) return rc;
     CK(cudaStreamSynchronize(ctx->stream));
@@ -305,7 +317,8 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     const size_t s_inner = al((size_t)b->n_inner * sizeof(MpInnerNode)), s_ibox = al((size_t)b->n_inner * sizeof(MpBox));
     const size_t s_pack = al((size_t)b->n_packets * sizeof(MpTrianglePacket)), s_pbox = al((size_t)b->n_packets * sizeof(MpBox));
     const size_t s_sh = al((size_t)b->n_packets * 8 * sizeof(MpTriShading)), s_v = al((size_t)b->n_vertices * sizeof(MpVertexShading));
-    const size_t total = 2 * s_inner + s_ibox + 2 * s_pack + s_pbox + s_sh + s_v + 256;
+    const size_t s_inner_w = al((size_t)b->n_inner * MPD_NODE_W * sizeof(float4)), s_pack_w = al((size_t)b->n_packets * MPD_PACK_W * sizeof(float4));
+    const size_t total = 2 * s_inner + s_ibox + 2 * s_pack + s_pbox + s_sh + s_v + s_inner_w + s_pack_w + 256;
     if (total > ctx->scene_blob_cap) {  // pooled contexts keep the allocation between renders
         if (ctx->d_scene_blob) CK(cudaFree(ctx->d_scene_blob));
         ctx->d_scene_blob = nullptr, ctx->scene_blob_cap = 0, ctx->has_scene = false;
@@ -350,6 +363,22 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     }
     ctx->scene_cm.inner_cm = (const uint4*)up(cm_inner.data(), cm_inner.size() * 4, s_inner);
     ctx->scene_cm.packets_cm = (const uint4*)up(cm_pack.data(), cm_pack.size() * 4, s_pack);
+    // decoded layout (trace.cuh): written on the device from the arrays just uploaded
+    float4* inner_w = (float4*)p;
+    p += s_inner_w;
+    float4* packets_w = (float4*)p;
+    p += s_pack_w;
+    ctx->scene.inner_w = inner_w, ctx->scene.packets_w = packets_w;
+    if (!ctx->d_flags) CK(cudaMalloc(&ctx->d_flags, sizeof(uint32_t)));
+    CK(cudaMemsetAsync(ctx->d_flags, 0, sizeof(uint32_t), ctx->stream));
+    if (b->n_inner) {
+        mpd::decode_inner_kernel<<<(unsigned)(((size_t)b->n_inner * 8 + 255) / 256), 256, 0, ctx->stream>>>(ctx->scene, b->n_inner, inner_w, ctx->d_flags);
+        ctx->launches++;
+    }
+    mpd::decode_packets_kernel<<<(unsigned)(((size_t)b->n_packets * 8 + 255) / 256), 256, 0, ctx->stream>>>(ctx->scene, b->n_packets, packets_w);
+    ctx->launches++;
+    uint32_t h_flags = 0;
+    CK(cudaMemcpyAsync(&h_flags, ctx->d_flags, sizeof h_flags, cudaMemcpyDeviceToHost, ctx->stream));
     ctx->scene.root = b->root;
     {  // extension integrator epsilon: 1e-4 * |bbox size|, same unfused arithmetic as the oracle
         V3 s = v3(b->bbox_max[0], b->bbox_max[1], b->bbox_max[2]) - v3(b->bbox_min[0], b->bbox_min[1], b->bbox_min[2]);
@@ -357,6 +386,7 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     }
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaGetLastError());
+    ctx->decoded_ok = h_flags == 0;  // a child box with min > max: stay on the quantised records
     ctx->max_stack = st.max_stack;
     ctx->has_scene = true;
     return MP_OK;

@@ -66,7 +66,7 @@ __device__ __forceinline__ bool map_pixel(const TileMap& tm, unsigned long long 
 }
 
 // Worker::render_sample (worker.rs:51-65) for max_bounces == 0; extension integrator otherwise.
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __device__ __forceinline__ float4 render_sample(const Scene& sc, const Camera& cam, uint32_t px, uint32_t py, uint32_t pixel_index,
                                                 uint32_t sample, uint32_t seed_hash, uint32_t max_bounces, ThreadCounts& tc) {
     uint32_t rng = rng_init(pixel_index, sample, seed_hash);
@@ -74,7 +74,7 @@ __device__ __forceinline__ float4 render_sample(const Scene& sc, const Camera& c
     tc.camera_rays++;
     if (max_bounces == 0) {
         tc.rays++;
-        const Hit h = trace<ORDER, COUNT>(sc, ray, false, tc.vis);
+        const Hit h = trace<LAYOUT, ORDER, COUNT>(sc, ray, false, tc.vis);
         if (h.tri == MP_NO_HIT) return make_float4(0.f, 0.f, 0.f, 0.f);
         const F3 n = shading_normal(sc, h);
         const float d = fabsf(dotn(ray.d, n));
@@ -83,7 +83,7 @@ __device__ __forceinline__ float4 render_sample(const Scene& sc, const Camera& c
     float T = 1.0f, L = 0.0f, alpha = 0.0f;
     for (uint32_t depth = 0;; ++depth) {
         tc.rays++;
-        const Hit h = trace<ORDER, COUNT>(sc, ray, false, tc.vis);
+        const Hit h = trace<LAYOUT, ORDER, COUNT>(sc, ray, false, tc.vis);
         if (h.tri == MP_NO_HIT) {
             L = __fadd_rn(L, __fmul_rn(T, EXT_ENV));
             break;
@@ -99,7 +99,7 @@ __device__ __forceinline__ float4 render_sample(const Scene& sc, const Camera& c
         if (c > 0.0f) {
             const Ray sray = ray_new(origin, sun);
             tc.rays++, tc.shadow_rays++;
-            const Hit sh = trace<ORDER, COUNT>(sc, sray, true, tc.vis);
+            const Hit sh = trace<LAYOUT, ORDER, COUNT>(sc, sray, true, tc.vis);
             if (sh.tri == MP_NO_HIT) L = __fadd_rn(L, __fmul_rn(__fmul_rn(T, EXT_SUN_E), c));
         }
         if (depth >= EXT_RR_START) {
@@ -122,7 +122,7 @@ __device__ __forceinline__ float4 render_sample(const Scene& sc, const Camera& c
 }
 
 // Worker::render_tile for many tiles (worker.rs:32-49): one thread per pixel, samples summed sequentially.
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) render_mega_kernel(Scene sc, Camera cam, TileMap tm, float4* __restrict__ film, uint32_t width,
                                                           uint32_t sample_base, uint32_t sample_count, uint32_t max_bounces,
                                                           uint32_t seed_hash, DevCounters* dc) {
@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(128) render_mega_kernel(Scene sc, Camera cam, 
         const uint32_t pixel_index = y * width + x;
         float4 sum = film[pixel_index];
         for (uint32_t s = 0; s < sample_count; ++s) {
-            const float4 c = render_sample<ORDER, COUNT>(sc, cam, x, y, pixel_index, sample_base + s, seed_hash, max_bounces, tc);
+            const float4 c = render_sample<LAYOUT, ORDER, COUNT>(sc, cam, x, y, pixel_index, sample_base + s, seed_hash, max_bounces, tc);
             sum.x = __fadd_rn(sum.x, c.x), sum.y = __fadd_rn(sum.y, c.y), sum.z = __fadd_rn(sum.z, c.z), sum.w = __fadd_rn(sum.w, c.w);
         }
         film[pixel_index] = sum;
@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(128) render_mega_kernel(Scene sc, Camera cam, 
 }
 
 // Object::intersect on caller-provided rays (the bit-exactness gate).  Rays are 36-byte AoS records.
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) trace_rays_kernel(Scene sc, const float* __restrict__ rays, unsigned long long n,
                                                          uint4* __restrict__ hits, DevCounters* dc) {
     const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(128) trace_rays_kernel(Scene sc, const float* 
         r.d = f3(__ldg(p + 3), __ldg(p + 4), __ldg(p + 5));
         r.inv = f3(__ldg(p + 6), __ldg(p + 7), __ldg(p + 8));
         tc.rays = 1;
-        const Hit h = trace<ORDER, COUNT>(sc, r, false, tc.vis);
+        const Hit h = trace<LAYOUT, ORDER, COUNT>(sc, r, false, tc.vis);
         hits[i] = make_uint4(h.tri, __float_as_uint(h.t), __float_as_uint(h.u), __float_as_uint(h.v));
     }
     flush_counts(dc, tc, COUNT);

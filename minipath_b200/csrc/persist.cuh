@@ -12,8 +12,13 @@
 
 namespace mpd {
 
-template <bool NANPATH>
-__device__ __forceinline__ void persist_inner(const Scene& sc, const Ray& r, uint32_t index, float max_t, uint2* stk, int& sp, int order) {
+// One inner node for one ray, either layout; `stk` is a stack view (LocalStack, or the pool's interleaved stacks).
+template <int LAYOUT, int ORDER, bool NANPATH, class S>
+__device__ __forceinline__ void persist_inner(const Scene& sc, const Ray& r, const RaySel& sel, uint32_t index, float max_t, const S& stk, int& sp) {
+    if (LAYOUT == MP_LAYOUT_DECODED) {
+        inner_decoded<ORDER, NANPATH>(sc, r, sel, index, max_t, stk, sp);
+        return;
+    }
     const float4 b0 = __ldg(sc.inner_box + 2 * (size_t)index), b1 = __ldg(sc.inner_box + 2 * (size_t)index + 1);
     const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
     const uint4* n = sc.inner + 8 * (size_t)index;
@@ -27,24 +32,35 @@ __device__ __forceinline__ void persist_inner(const Scene& sc, const Ray& r, uin
     for (int lane = 0; lane < 8; ++lane) {
         if (links[lane] == MP_LINK_NULL) continue;  // discarded when popped (:49); skipping is neutral
         float t1;
-        if (child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1)) {
-            if (order == MP_ORDER_NEAR_FIRST) {
-                int pos = sp;
-                while (pos > base && __uint_as_float(stk[pos - 1].y) <= t1) {
-                    stk[pos] = stk[pos - 1];
-                    --pos;
-                }
-                stk[pos] = make_uint2(links[lane], __float_as_uint(t1));
-                ++sp;
-            } else {
-                stk[sp++] = make_uint2(links[lane], __float_as_uint(t1));  // lane order: lane 7 pops first (:161)
-            }
+        if (child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1)) push_child<ORDER>(stk, base, sp, links[lane], t1);
+    }
+}
+
+// One packet of a leaf for one ray, either layout (ray_bvh_intersection.rs:104-141).
+template <int LAYOUT>
+__device__ __forceinline__ void persist_packet(const Scene& sc, const Ray& r, uint32_t pidx, float max_t, Hit& local) {
+    if (LAYOUT == MP_LAYOUT_DECODED) {
+        packet_decoded(sc, r, pidx, max_t, local);
+        return;
+    }
+    const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)pidx), b1 = __ldg(sc.packet_box + 2 * (size_t)pidx + 1);
+    const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
+    const uint4* pk = sc.packets + 9 * (size_t)pidx;
+    uint4 q[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) q[k] = __ldg(pk + k);
+#pragma unroll
+    for (int lane = 0; lane < 8; ++lane) {
+        float t, u, v;
+        if (tri_lane(q, lane, bmin, bsize, r, max_t, t, u, v) && t < local.t) {
+            local.t = t, local.u = u, local.v = v;
+            local.tri = pidx * 8u + (uint32_t)lane;
         }
     }
 }
 
 // fetch(i, r) loads ray i completely (o, d, inv); emit(i, best) stores its result.
-template <int ORDER, bool COUNT, class Fetch, class Emit>
+template <int LAYOUT, int ORDER, bool COUNT, class Fetch, class Emit>
 __device__ __forceinline__ void persist_run(const Scene& sc, uint32_t n, uint32_t first, uint32_t stride, bool any_hit, Fetch fetch, Emit emit,
                                             ThreadCounts& tc) {
     constexpr uint32_t FULL = 0xffffffffu;
@@ -53,6 +69,7 @@ __device__ __forceinline__ void persist_run(const Scene& sc, uint32_t n, uint32_
     uint32_t cur = 0, next = first;
     bool have = false, nanpath = false;
     Ray r{};
+    RaySel sel{};
     Hit best{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
     uint32_t kind = 0;  // 0 nothing popped, 1 inner node pending, 2 leaf in progress
     uint32_t p_index = 0, lf_rem = 0;
@@ -70,7 +87,8 @@ __device__ __forceinline__ void persist_run(const Scene& sc, uint32_t n, uint32_
                 if (next >= n) break;
                 cur = next, next += stride;
                 fetch(cur, r);
-                nanpath = (fabsf(r.inv.x) == MPD_INF) | (fabsf(r.inv.y) == MPD_INF) | (fabsf(r.inv.z) == MPD_INF);
+                nanpath = ray_needs_nanpath(r);
+                if (LAYOUT == MP_LAYOUT_DECODED) sel = ray_sel(r);
                 best = Hit{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
                 stk[0] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
                 sp = 1;
@@ -95,27 +113,14 @@ __device__ __forceinline__ void persist_run(const Scene& sc, uint32_t n, uint32_
             if (kind == 1) {
                 if (COUNT) tc.vis.inner++;
                 if (nanpath)
-                    persist_inner<true>(sc, r, p_index, best.t, stk, sp, ORDER);
+                    persist_inner<LAYOUT, ORDER, true>(sc, r, sel, p_index, best.t, LocalStack{stk}, sp);
                 else
-                    persist_inner<false>(sc, r, p_index, best.t, stk, sp, ORDER);
+                    persist_inner<LAYOUT, ORDER, false>(sc, r, sel, p_index, best.t, LocalStack{stk}, sp);
                 kind = 0;
             }
         } else if (kind == 2) {
             // ---- one packet of the leaf (ray_bvh_intersection.rs:104-141) ----
-            const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)p_index), b1 = __ldg(sc.packet_box + 2 * (size_t)p_index + 1);
-            const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
-            const uint4* pk = sc.packets + 9 * (size_t)p_index;
-            uint4 q[9];
-#pragma unroll
-            for (int k = 0; k < 9; ++k) q[k] = __ldg(pk + k);
-#pragma unroll
-            for (int lane = 0; lane < 8; ++lane) {
-                float t, u, v;
-                if (tri_lane(q, lane, bmin, bsize, r, lf_max_t, t, u, v) && t < lf_local.t) {
-                    lf_local.t = t, lf_local.u = u, lf_local.v = v;
-                    lf_local.tri = p_index * 8u + (uint32_t)lane;
-                }
-            }
+            persist_packet<LAYOUT>(sc, r, p_index, lf_max_t, lf_local);
             ++p_index;
             if (--lf_rem == 0) {
                 kind = 0;
@@ -130,11 +135,11 @@ __device__ __forceinline__ void persist_run(const Scene& sc, uint32_t n, uint32_
 
 // ---- kernels: persistent grid (resident blocks x SMs), lane-strided over the queue ----
 
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) trace_rays_persist_kernel(Scene sc, const float* __restrict__ rays, uint32_t n, uint4* __restrict__ hits,
                                                                  DevCounters* dc) {
     ThreadCounts tc{};
-    persist_run<ORDER, COUNT>(
+    persist_run<LAYOUT, ORDER, COUNT>(
         sc, n, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x, false,
         [&](uint32_t i, Ray& r) {
             const float* p = rays + 9 * (size_t)i;
@@ -146,13 +151,13 @@ __global__ void __launch_bounds__(128) trace_rays_persist_kernel(Scene sc, const
     flush_counts(dc, tc, COUNT);
 }
 
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) wf_trace_persist_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
                                                                const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
                                                                uint4* __restrict__ hit, DevCounters* dc) {
     ThreadCounts tc{};
     uint32_t path = 0;
-    persist_run<ORDER, COUNT>(
+    persist_run<LAYOUT, ORDER, COUNT>(
         sc, *count, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x, false,
         [&](uint32_t i, Ray& r) {
             path = queue[i];
@@ -162,13 +167,13 @@ __global__ void __launch_bounds__(128) wf_trace_persist_kernel(Scene sc, const u
     flush_counts(dc, tc, COUNT);
 }
 
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) wf_shadow_persist_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
                                                                 const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, DevCounters* dc) {
     ThreadCounts tc{};
     float contribution = 0.0f;
     const Ray sun = ray_new(f3(0.f, 0.f, 0.f), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
-    persist_run<ORDER, COUNT>(
+    persist_run<LAYOUT, ORDER, COUNT>(
         sc, *sh_count, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x, true,
         [&](uint32_t i, Ray& r) {
             const float4 o = sh_o[i];

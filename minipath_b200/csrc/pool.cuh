@@ -34,6 +34,13 @@ struct PoolWarp {  // shared-memory view of one warp's pool
 enum { PC_OX, PC_OY, PC_OZ, PC_DX, PC_DY, PC_DZ, PC_IX, PC_IY, PC_IZ, PC_BT, PC_BU, PC_BV, PC_BTRI, PC_SP, PC_RID, PC_PIDX, PC_REM,
        PC_LMAX, PC_LT, PC_LU, PC_LV, PC_LTRI };
 
+// The stacks of a warp's 96 rays are interleaved entry-major in the global scratch ([entry][slot]): lanes working on rays at a
+// similar depth touch neighbouring 8-byte words instead of 96 separate regions.
+struct PoolStack {
+    uint2* p;  // entry 0 of this slot
+    __device__ __forceinline__ uint2& at(int i) const { return p[(size_t)i * POOL_W]; }
+};
+
 struct PoolQueues {  // warp-uniform ring cursors
     uint32_t head[3], tail[3];
     __device__ __forceinline__ uint32_t size(int q) const { return tail[q] - head[q]; }
@@ -48,12 +55,12 @@ __device__ __forceinline__ void pool_push(const PoolWarp& pw, PoolQueues& qs, in
 
 // Pop the ray's next surviving entry and file the slot; `active` lanes own `slot` with current (sp, best_t).
 template <bool COUNT, class Emit>
-__device__ __forceinline__ void pool_advance(const PoolWarp& pw, PoolQueues& qs, bool active, uint32_t slot, uint2* stk, int sp, float best_t,
+__device__ __forceinline__ void pool_advance(const PoolWarp& pw, PoolQueues& qs, bool active, uint32_t slot, const PoolStack stk, int sp, float best_t,
                                              Emit emit, ThreadCounts& tc) {
     uint32_t kind = 0;  // 0 finished, 1 inner, 2 leaf
     if (active) {
         while (sp > 0) {
-            const uint2 e = stk[--sp];
+            const uint2 e = stk.at(--sp);
             if (__uint_as_float(e.y) > best_t) continue;  // ray_bvh_intersection.rs:40
             const uint32_t count = e.x & MP_LINK_COUNT_MASK;
             pw.u(PC_PIDX, slot) = e.x >> MP_LINK_COUNT_BITS;
@@ -88,7 +95,7 @@ __device__ __forceinline__ Ray pool_load_ray(const PoolWarp& pw, uint32_t s) {
 
 // fetch(i, r) loads ray i completely (o, d, inv); emit(i, hit) stores its result.  `claim` is a zeroed device counter shared by
 // the launch: warps claim 32 consecutive rays at a time.  `scratch` holds gridDim.x * POOL_WARPS * POOL_W stacks of stack_cap entries.
-template <int ORDER, bool COUNT, class Fetch, class Emit>
+template <int LAYOUT, int ORDER, bool COUNT, class Fetch, class Emit>
 __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* claim, bool any_hit, uint2* __restrict__ scratch, uint32_t stack_cap,
                                          unsigned char* smem, Fetch fetch, Emit emit, ThreadCounts& tc) {
     constexpr uint32_t FULL = 0xffffffffu;
@@ -124,11 +131,11 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
                 pw.f(PC_IX, slot) = r.inv.x, pw.f(PC_IY, slot) = r.inv.y, pw.f(PC_IZ, slot) = r.inv.z;
                 pw.f(PC_BT, slot) = MPD_FLT_MAX, pw.f(PC_BU, slot) = 0.0f, pw.f(PC_BV, slot) = 0.0f, pw.u(PC_BTRI, slot) = MP_NO_HIT;
                 pw.u(PC_RID, slot) = base + lane;
-                wstacks[(size_t)slot * stack_cap] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
+                wstacks[slot] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
                 tc.rays++;
             }
             qs.head[2] += got;
-            pool_advance<COUNT>(pw, qs, act, slot, wstacks + (size_t)slot * stack_cap, 1, MPD_FLT_MAX, emit, tc);
+            pool_advance<COUNT>(pw, qs, act, slot, PoolStack{wstacks + slot}, 1, MPD_FLT_MAX, emit, tc);
             __syncwarp();
             continue;
         }
@@ -141,20 +148,22 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
             uint32_t slot = 0;
             int sp = 0;
             float bt = 0.0f;
-            uint2* stk = wstacks;
+            PoolStack stk{wstacks};
             if (act) {
                 slot = pw.ring[0 * POOL_RING + ((qs.head[0] + lane) & (POOL_RING - 1))];
-                stk = wstacks + (size_t)slot * stack_cap;
+                stk.p = wstacks + slot;
                 const Ray r = pool_load_ray(pw, slot);
                 bt = pw.f(PC_BT, slot);
                 sp = (int)pw.u(PC_SP, slot);
                 const uint32_t node = pw.u(PC_PIDX, slot);
                 if (COUNT) tc.vis.inner++;
-                const bool nanpath = (fabsf(r.inv.x) == MPD_INF) | (fabsf(r.inv.y) == MPD_INF) | (fabsf(r.inv.z) == MPD_INF);
-                if (nanpath)
-                    persist_inner<true>(sc, r, node, bt, stk, sp, ORDER);
-                else
-                    persist_inner<false>(sc, r, node, bt, stk, sp, ORDER);
+                if (ray_needs_nanpath(r)) {
+                    persist_inner<LAYOUT, ORDER, true>(sc, r, RaySel{}, node, bt, stk, sp);
+                } else {
+                    RaySel sel{};
+                    if (LAYOUT == MP_LAYOUT_DECODED) sel = ray_sel(r);
+                    persist_inner<LAYOUT, ORDER, false>(sc, r, sel, node, bt, stk, sp);
+                }
             }
             qs.head[0] += take;
             pool_advance<COUNT>(pw, qs, act, slot, stk, sp, bt, emit, tc);
@@ -165,29 +174,16 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
             uint32_t slot = 0;
             int sp = 0;
             float bt = 0.0f;
-            uint2* stk = wstacks;
+            PoolStack stk{wstacks};
             bool done = false;  // the leaf's last packet has been tested
             if (act) {
                 slot = pw.ring[1 * POOL_RING + ((qs.head[1] + lane) & (POOL_RING - 1))];
-                stk = wstacks + (size_t)slot * stack_cap;
+                stk.p = wstacks + slot;
                 const Ray r = pool_load_ray(pw, slot);
                 uint32_t pidx = pw.u(PC_PIDX, slot), rem = pw.u(PC_REM, slot);
                 const float max_t = pw.f(PC_LMAX, slot);
                 Hit local{pw.f(PC_LT, slot), pw.f(PC_LU, slot), pw.f(PC_LV, slot), pw.u(PC_LTRI, slot)};
-                const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)pidx), b1 = __ldg(sc.packet_box + 2 * (size_t)pidx + 1);
-                const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
-                const uint4* pk = sc.packets + 9 * (size_t)pidx;
-                uint4 q[9];
-#pragma unroll
-                for (int k = 0; k < 9; ++k) q[k] = __ldg(pk + k);
-#pragma unroll
-                for (int tl = 0; tl < 8; ++tl) {
-                    float t, u, v;
-                    if (tri_lane(q, tl, bmin, bsize, r, max_t, t, u, v) && t < local.t) {
-                        local.t = t, local.u = u, local.v = v;
-                        local.tri = pidx * 8u + (uint32_t)tl;
-                    }
-                }
+                persist_packet<LAYOUT>(sc, r, pidx, max_t, local);
                 ++pidx, --rem;
                 pw.u(PC_PIDX, slot) = pidx, pw.u(PC_REM, slot) = rem;
                 sp = (int)pw.u(PC_SP, slot);
@@ -213,12 +209,12 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
 
 // ---- kernels: 128 threads = 4 pools per block, persistent grid ----
 
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) trace_rays_pool_kernel(Scene sc, const float* __restrict__ rays, uint32_t n, uint4* __restrict__ hits,
                                                               DevCounters* dc, uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];
     ThreadCounts tc{};
-    pool_run<ORDER, COUNT>(
+    pool_run<LAYOUT, ORDER, COUNT>(
         sc, n, claim, false, scratch, stack_cap, pool_smem,
         [&](uint32_t i, Ray& r) {
             const float* p = rays + 9 * (size_t)i;
@@ -230,14 +226,14 @@ __global__ void __launch_bounds__(128) trace_rays_pool_kernel(Scene sc, const fl
     flush_counts(dc, tc, COUNT);
 }
 
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) wf_trace_pool_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
                                                             const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
                                                             uint4* __restrict__ hit, DevCounters* dc, uint32_t* claim, uint2* scratch,
                                                             uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];
     ThreadCounts tc{};
-    pool_run<ORDER, COUNT>(
+    pool_run<LAYOUT, ORDER, COUNT>(
         sc, *count, claim, false, scratch, stack_cap, pool_smem,
         [&](uint32_t i, Ray& r) {
             const uint32_t path = queue[i];
@@ -247,14 +243,14 @@ __global__ void __launch_bounds__(128) wf_trace_pool_kernel(Scene sc, const uint
     flush_counts(dc, tc, COUNT);
 }
 
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) wf_shadow_pool_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
                                                              const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, DevCounters* dc,
                                                              uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];
     ThreadCounts tc{};
     const Ray sun = ray_new(f3(0.f, 0.f, 0.f), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
-    pool_run<ORDER, COUNT>(
+    pool_run<LAYOUT, ORDER, COUNT>(
         sc, *sh_count, claim, true, scratch, stack_cap, pool_smem,
         [&](uint32_t i, Ray& r) {
             const float4 o = sh_o[i];

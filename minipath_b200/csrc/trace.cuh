@@ -25,6 +25,8 @@ struct Scene {
     const float4* __restrict__ packet_box;
     const uint4* __restrict__ tri_shading;
     const float4* __restrict__ vertices;
+    const float4* __restrict__ inner_w;    // decoded nodes (MP_LAYOUT_DECODED), MPD_NODE_W float4 each
+    const float4* __restrict__ packets_w;  // decoded packets, MPD_PACK_W float4 each
     uint32_t root;
     float eps;  // extension integrator: origin offset, 1e-4 * scene diagonal
 };
@@ -93,12 +95,145 @@ __device__ __forceinline__ bool tri_lane(const uint4 (&q)[9], int lane, const F3
     return u >= 0.0f && v >= 0.0f && __fadd_rn(u, v) <= 1.0f && t >= 0.0f && t <= max_t;
 }
 
-template <int ORDER, bool COUNT, bool NANPATH>
+// ---- MP_LAYOUT_DECODED: the same nodes with the u16 -> f32 dequantisation hoisted out of the traversal ----
+// The traversal kernels are bound by instruction issue, not by bytes (profiles/r1_wf_trace_thread.txt: 70 % issue slots busy,
+// L2 at 4 %), and 18 of the ~46 instructions a child costs are its six dequantisations (PRMT + 2 FFMA each).  Every child
+// coordinate only depends on the node's enclosing box and its quantised bounds, so `decode_scene_kernel` evaluates
+// fma(size, float(q) * K, min) ONCE per scene with the same device function and stores the f32 result; the traversal then reads
+//   inner_w[i]   16 x float4: min.x[8] min.y[8] min.z[8] max.x[8] max.y[8] max.z[8] links[8] pad[8]          (256 B)
+//   packets_w[p] 18 x float4: v0.x[8] v0.y[8] v0.z[8] e1.x[8] e1.y[8] e1.z[8] e2.x[8] e2.y[8] e2.z[8]        (288 B)
+// with e1 = v1 - v0, e2 = v2 - v0 (the unfused subtractions of triangle.rs:193-194).  Same operations on the same operands
+// → the same bits as decoding per visit.  NULL children are stored as min = +inf, max = -inf so that they fail the slab test.
+#define MPD_NODE_W 16
+#define MPD_PACK_W 18
+
+// A ray whose inverse direction is finite and non-NaN crosses the planes of a child box in a known order: (b - o) * inv is
+// monotonic in b, so min(lo, hi) is the plane on the side the ray comes from.  Decoded nodes keep min <= max per axis
+// (checked by decode_scene_kernel), hence the near / far rows can be picked per RAY instead of per child with 6 min/max.
+struct RaySel {
+    uint32_t nx, ny, nz, fx, fy, fz;  // float4 row offsets inside a decoded node
+};
+__device__ __forceinline__ RaySel ray_sel(const Ray& r) {
+    RaySel s;
+    const bool sx = r.inv.x < 0.0f, sy = r.inv.y < 0.0f, sz = r.inv.z < 0.0f;
+    s.nx = sx ? 6u : 0u, s.fx = sx ? 0u : 6u;
+    s.ny = sy ? 8u : 2u, s.fy = sy ? 2u : 8u;
+    s.nz = sz ? 10u : 4u, s.fz = sz ? 4u : 10u;
+    return s;
+}
+// Rays that need the reference's NaN handling (aabb.rs:262-267) or are not finite at all take the general path.
+__device__ __forceinline__ bool ray_needs_nanpath(const Ray& r) {
+    return !(fabsf(r.inv.x) < MPD_INF) | !(fabsf(r.inv.y) < MPD_INF) | !(fabsf(r.inv.z) < MPD_INF) | !(fabsf(r.o.x) < MPD_INF) |
+           !(fabsf(r.o.y) < MPD_INF) | !(fabsf(r.o.z) < MPD_INF);
+}
+
+__device__ __forceinline__ float comp(const float4& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w)); }
+__device__ __forceinline__ uint32_t comp(const uint4& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w)); }
+
+// Stack views: thread-per-ray kernels index a private array, the pool kernel interleaves the stacks of a warp's rays.
+struct LocalStack {
+    uint2* p;
+    __device__ __forceinline__ uint2& at(int i) const { return p[i]; }
+};
+
+template <int ORDER, class S>
+__device__ __forceinline__ void push_child(const S& stk, int base, int& sp, uint32_t link, float t1) {
+    if (ORDER == MP_ORDER_NEAR_FIRST) {
+        // keep this node's entries sorted far → near (ties: lower lane nearer the top)
+        int pos = sp;
+        while (pos > base && __uint_as_float(stk.at(pos - 1).y) <= t1) {
+            stk.at(pos) = stk.at(pos - 1);
+            --pos;
+        }
+        stk.at(pos) = make_uint2(link, __float_as_uint(t1));
+        ++sp;
+    } else {
+        stk.at(sp++) = make_uint2(link, __float_as_uint(t1));  // lane order: lane 7 pops first (:161)
+    }
+}
+
+// InnerNode::intersect on a decoded node (ray_bvh_intersection.rs:149-162).
+template <int ORDER, bool NANPATH, class S>
+__device__ __forceinline__ void inner_decoded(const Scene& sc, const Ray& r, const RaySel& sel, uint32_t index, float max_t, const S& stk, int& sp) {
+    const float4* n = sc.inner_w + MPD_NODE_W * (size_t)index;
+    const int base = sp;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {  // children 4h .. 4h+3
+        const uint4 lk = __ldg(reinterpret_cast<const uint4*>(n + 12 + h));
+        if (NANPATH) {
+            const float4 ax = __ldg(n + 0 + h), ay = __ldg(n + 2 + h), az = __ldg(n + 4 + h);
+            const float4 bx = __ldg(n + 6 + h), by = __ldg(n + 8 + h), bz = __ldg(n + 10 + h);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (comp(lk, k) == MP_LINK_NULL) continue;
+                float lox = __fmul_rn(__fsub_rn(comp(ax, k), r.o.x), r.inv.x), loy = __fmul_rn(__fsub_rn(comp(ay, k), r.o.y), r.inv.y);
+                float loz = __fmul_rn(__fsub_rn(comp(az, k), r.o.z), r.inv.z), hix = __fmul_rn(__fsub_rn(comp(bx, k), r.o.x), r.inv.x);
+                float hiy = __fmul_rn(__fsub_rn(comp(by, k), r.o.y), r.inv.y), hiz = __fmul_rn(__fsub_rn(comp(bz, k), r.o.z), r.inv.z);
+                if (lox != lox) lox = MPD_NINF;
+                if (loy != loy) loy = MPD_NINF;
+                if (loz != loz) loz = MPD_NINF;
+                if (hix != hix) hix = MPD_INF;
+                if (hiy != hiy) hiy = MPD_INF;
+                if (hiz != hiz) hiz = MPD_INF;
+                const float cminx = minps(lox, hix), cminy = minps(loy, hiy), cminz = minps(loz, hiz);
+                const float cmaxx = maxps(lox, hix), cmaxy = maxps(loy, hiy), cmaxz = maxps(loz, hiz);
+                const float t1 = maxps(maxps(cminx, 0.0f), maxps(cminy, cminz));
+                const float t2 = minps(minps(cmaxx, max_t), minps(cmaxy, cmaxz));
+                if (t1 <= t2) push_child<ORDER>(stk, base, sp, comp(lk, k), t1);
+            }
+        } else {
+            const float4 ax = __ldg(n + sel.nx + h), ay = __ldg(n + sel.ny + h), az = __ldg(n + sel.nz + h);
+            const float4 bx = __ldg(n + sel.fx + h), by = __ldg(n + sel.fy + h), bz = __ldg(n + sel.fz + h);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float lox = __fmul_rn(__fsub_rn(comp(ax, k), r.o.x), r.inv.x), loy = __fmul_rn(__fsub_rn(comp(ay, k), r.o.y), r.inv.y);
+                const float loz = __fmul_rn(__fsub_rn(comp(az, k), r.o.z), r.inv.z), hix = __fmul_rn(__fsub_rn(comp(bx, k), r.o.x), r.inv.x);
+                const float hiy = __fmul_rn(__fsub_rn(comp(by, k), r.o.y), r.inv.y), hiz = __fmul_rn(__fsub_rn(comp(bz, k), r.o.z), r.inv.z);
+                const float t1 = fmaxf(fmaxf(lox, loy), fmaxf(loz, 0.0f));    // FMNMX3 + FMNMX
+                const float t2 = fminf(fminf(hix, hiy), fminf(hiz, max_t));
+                if (t1 <= t2) push_child<ORDER>(stk, base, sp, comp(lk, k), t1);  // NULL children: t1 = +inf, t2 = -inf
+            }
+        }
+    }
+}
+
+// One decoded packet: Triangle<WorldPoint8>::intersect + the t-range mask (triangle.rs:187-216; ray_bvh_intersection.rs:125-134).
+__device__ __forceinline__ void packet_decoded(const Scene& sc, const Ray& r, uint32_t pidx, float max_t, Hit& local) {
+    const float4* pk = sc.packets_w + MPD_PACK_W * (size_t)pidx;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {  // triangles 4h .. 4h+3
+        float4 c[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) c[k] = __ldg(pk + 2 * k + h);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const F3 v0 = f3(comp(c[0], k), comp(c[1], k), comp(c[2], k));
+            const F3 e1 = f3(comp(c[3], k), comp(c[4], k), comp(c[5], k));
+            const F3 e2 = f3(comp(c[6], k), comp(c[7], k), comp(c[8], k));
+            const F3 p = fma_cross(r.d, e2);
+            const float det = fma_dot(e1, p);
+            const float inv = __frcp_rn(det);  // correctly rounded 1/det = the reference's division; may be infinite
+            const F3 s = r.o - v0;
+            const float u = __fmul_rn(inv, fma_dot(s, p));
+            const F3 qv = fma_cross(s, e1);
+            const float v = __fmul_rn(inv, fma_dot(r.d, qv));
+            const float t = __fmul_rn(inv, fma_dot(e2, qv));
+            if (u >= 0.0f && v >= 0.0f && __fadd_rn(u, v) <= 1.0f && t >= 0.0f && t <= max_t && t < local.t) {
+                local.t = t, local.u = u, local.v = v;
+                local.tri = pidx * 8u + (uint32_t)(4 * h + k);
+            }
+        }
+    }
+}
+
+template <int LAYOUT, int ORDER, bool COUNT, bool NANPATH>
 __device__ __forceinline__ Hit trace_impl(const Scene& sc, const Ray& r, bool any_hit, Visits& vis) {
     uint2 stk[MPD_STACK_MAX];  // (link, t1 bits)
     int sp = 0;
     stk[sp++] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
     Hit best{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
+    RaySel sel{};
+    if (LAYOUT == MP_LAYOUT_DECODED && !NANPATH) sel = ray_sel(r);
 
     while (sp > 0) {
         uint2 e = stk[--sp];
@@ -107,6 +242,10 @@ __device__ __forceinline__ Hit trace_impl(const Scene& sc, const Ray& r, bool an
         if (count == 0) {
             // ---- inner node (ray_bvh_intersection.rs:149-162) ----
             if (COUNT) vis.inner++;
+            if (LAYOUT == MP_LAYOUT_DECODED) {
+                inner_decoded<ORDER, NANPATH>(sc, r, sel, index, best.t, LocalStack{stk}, sp);
+                continue;
+            }
             const float4 b0 = __ldg(sc.inner_box + 2 * (size_t)index), b1 = __ldg(sc.inner_box + 2 * (size_t)index + 1);
             const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
             const uint4* n = sc.inner + 8 * (size_t)index;
@@ -122,39 +261,30 @@ __device__ __forceinline__ Hit trace_impl(const Scene& sc, const Ray& r, bool an
                 // NULL children have all-zero bounds and are discarded when popped (:49); skipping them is neutral
                 if (links[lane] == MP_LINK_NULL) continue;
                 float t1;
-                if (child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1)) {
-                    if (ORDER == MP_ORDER_NEAR_FIRST) {
-                        // keep this node's entries sorted far → near (ties: lower lane nearer the top)
-                        int pos = sp;
-                        while (pos > base && __uint_as_float(stk[pos - 1].y) <= t1) {
-                            stk[pos] = stk[pos - 1];
-                            --pos;
-                        }
-                        stk[pos] = make_uint2(links[lane], __float_as_uint(t1));
-                        ++sp;
-                    } else {
-                        stk[sp++] = make_uint2(links[lane], __float_as_uint(t1));  // lane order: lane 7 pops first
-                    }
-                }
+                if (child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1)) push_child<ORDER>(LocalStack{stk}, base, sp, links[lane], t1);
             }
         } else {
             // ---- leaf: ≤7 packets of 8 triangles (ray_bvh_intersection.rs:104-141) ----
             if (COUNT) vis.leaves++, vis.packets += count;
-            const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)index), b1 = __ldg(sc.packet_box + 2 * (size_t)index + 1);
-            const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
             const float max_t = best.t;  // not updated inside the leaf
             Hit local{MPD_INF, 0.0f, 0.0f, MP_NO_HIT};
-            for (uint32_t j = 0; j < count; ++j) {
-                const uint4* pk = sc.packets + 9 * (size_t)(index + j);
-                uint4 q[9];
+            if (LAYOUT == MP_LAYOUT_DECODED) {
+                for (uint32_t j = 0; j < count; ++j) packet_decoded(sc, r, index + j, max_t, local);
+            } else {
+                const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)index), b1 = __ldg(sc.packet_box + 2 * (size_t)index + 1);
+                const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
+                for (uint32_t j = 0; j < count; ++j) {
+                    const uint4* pk = sc.packets + 9 * (size_t)(index + j);
+                    uint4 q[9];
 #pragma unroll
-                for (int k = 0; k < 9; ++k) q[k] = __ldg(pk + k);
+                    for (int k = 0; k < 9; ++k) q[k] = __ldg(pk + k);
 #pragma unroll
-                for (int lane = 0; lane < 8; ++lane) {
-                    float t, u, v;
-                    if (tri_lane(q, lane, bmin, bsize, r, max_t, t, u, v) && t < local.t) {
-                        local.t = t, local.u = u, local.v = v;
-                        local.tri = (index + j) * 8u + (uint32_t)lane;
+                    for (int lane = 0; lane < 8; ++lane) {
+                        float t, u, v;
+                        if (tri_lane(q, lane, bmin, bsize, r, max_t, t, u, v) && t < local.t) {
+                            local.t = t, local.u = u, local.v = v;
+                            local.tri = (index + j) * 8u + (uint32_t)lane;
+                        }
                     }
                 }
             }
@@ -167,12 +297,11 @@ __device__ __forceinline__ Hit trace_impl(const Scene& sc, const Ray& r, bool an
     return best;
 }
 
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __device__ __forceinline__ Hit trace(const Scene& sc, const Ray& r, bool any_hit, Visits& vis) {
     // |inv| is infinite for a zero (or denormal) direction component
-    const bool nanpath = (fabsf(r.inv.x) == MPD_INF) | (fabsf(r.inv.y) == MPD_INF) | (fabsf(r.inv.z) == MPD_INF);
-    if (nanpath) return trace_impl<ORDER, COUNT, true>(sc, r, any_hit, vis);
-    return trace_impl<ORDER, COUNT, false>(sc, r, any_hit, vis);
+    if (ray_needs_nanpath(r)) return trace_impl<LAYOUT, ORDER, COUNT, true>(sc, r, any_hit, vis);
+    return trace_impl<LAYOUT, ORDER, COUNT, false>(sc, r, any_hit, vis);
 }
 
 // Hit finalisation (ray_bvh_intersection.rs:66-95): shading normal, normalised.

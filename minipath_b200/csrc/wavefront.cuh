@@ -108,7 +108,7 @@ __device__ __forceinline__ Ray load_ray(const float4 o, const float4 d) {
 }
 
 // Stage 2: closest-hit traversal of the queued paths.
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) wf_trace_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
                                                        const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
                                                        uint4* __restrict__ hit, DevCounters* dc) {
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(128) wf_trace_kernel(Scene sc, const uint32_t*
         const uint32_t path = queue[i];
         const Ray r = load_ray(ray_o[path], ray_d[path]);
         tc.rays = 1;
-        const Hit h = trace<ORDER, COUNT>(sc, r, false, tc.vis);
+        const Hit h = trace<LAYOUT, ORDER, COUNT>(sc, r, false, tc.vis);
         hit[path] = make_uint4(h.tri, __float_as_uint(h.t), __float_as_uint(h.u), __float_as_uint(h.v));
     }
     flush_counts(dc, tc, COUNT);
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(Scene sc, const uint32_t*
 }
 
 // Stage 3b: any-hit traversal of the light-sampling rays; unoccluded ones add their contribution to the path.
-template <int ORDER, bool COUNT>
+template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) wf_shadow_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
                                                         const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, DevCounters* dc) {
     const uint32_t n = *sh_count;
@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(128) wf_shadow_kernel(Scene sc, const float4* 
         const float4 o = sh_o[i];
         const Ray r = ray_new(f3(o.x, o.y, o.z), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
         tc.rays = 1, tc.shadow_rays = 1;
-        const Hit h = trace<ORDER, COUNT>(sc, r, true, tc.vis);
+        const Hit h = trace<LAYOUT, ORDER, COUNT>(sc, r, true, tc.vis);
         if (h.tri == MP_NO_HIT) {
             const uint32_t path = sh_path[i];
             ray_d[path].w = __fadd_rn(ray_d[path].w, o.w);
