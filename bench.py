@@ -52,7 +52,7 @@ def parse_args():
                     help="megakernel: one thread per pixel; wavefront-*: staged kernels with the thread-per-ray, the 8-lanes-per-ray "
                          "(octet) or the persistent phased thread-per-ray traversal kernel")
     ap.add_argument("--order", default="reference", choices=["reference", "near_first"])
-    ap.add_argument("--layout", default="decoded", choices=["decoded", "quantised"],
+    ap.add_argument("--layout", default="auto", choices=["auto", "decoded", "quantised"],
                     help="node layout read by the traversal kernels: f32 boxes/edges decoded at upload (default) or the reference's u16 records")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel")
     ap.add_argument("--bounces", type=int, default=-1, help="override the workload's max_bounces")
@@ -229,7 +229,7 @@ def run_b200(args, rank, local, world):
     stream = torch.cuda.Stream()
     ctx = mp.Context(local)
     ctx.set_stream(stream.cuda_stream)
-    ctx.set_node_layout(mp.LAYOUT_DECODED if args.layout == "decoded" else mp.LAYOUT_QUANTISED)
+    ctx.set_node_layout({"auto": mp.LAYOUT_AUTO, "decoded": mp.LAYOUT_DECODED, "quantised": mp.LAYOUT_QUANTISED}[args.layout])
     ctx.upload_scene(bvh)
     ctx.set_camera(sampler)
     film = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")

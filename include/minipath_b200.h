@@ -225,13 +225,16 @@ int mp_ctx_sync(MpCtx* ctx);
 #define MP_TRACE_HYBRID_POOL 5u
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant);
 /* Node layout the THREAD / PERSIST / POOL kernels and the megakernel read (same results, bit for bit):
- * QUANTISED = the reference records as they are (InnerNode 128 B, RelativeTriangle8 144 B; u16 → f32 on every visit,
- *             compressed_geometry.rs:95-110,160-162);
+ * QUANTISED = the reference records (InnerNode 128 B, RelativeTriangle8 144 B; u16 → f32 on every visit,
+ *             compressed_geometry.rs:95-110,160-162), each interleaved with its enclosing box into one 160 B / 192 B record
+ *             that a lane gathers with 256-bit loads — fewest bytes per visit, best for incoherent rays (L1-bound gathers);
  * DECODED   = the dequantisation hoisted to upload time: f32 child boxes (256 B per node) and f32 v0 / e1 / e2 per triangle
- *             (288 B per packet), written once by a device kernel with the same fma — default, ~2x fewer instructions per visit.
- * Takes effect at the next mp_scene_upload only for the memory it allocates; switching is allowed at any time. */
+ *             (288 B per packet), written once by a device kernel with the same fma — ~2x fewer instructions per visit, best
+ *             for coherent rays (issue-bound);
+ * AUTO      = DECODED for the thread-per-ray kernels on camera rays and the megakernel, QUANTISED for PERSIST / POOL (default). */
 #define MP_LAYOUT_QUANTISED 0u
 #define MP_LAYOUT_DECODED 1u
+#define MP_LAYOUT_AUTO 2u
 int mp_ctx_set_node_layout(MpCtx* ctx, uint32_t layout);
 /* Count traversal work (adds a few atomics per warp); off by default. */
 int mp_ctx_enable_counters(MpCtx* ctx, int on);

@@ -12,6 +12,7 @@ import numpy as np
 
 from . import _ffi
 from ._ffi import (  # noqa: F401  (re-exported)
+    LAYOUT_AUTO,
     LAYOUT_DECODED,
     LAYOUT_QUANTISED,
     MODE_MEGAKERNEL,
@@ -409,7 +410,7 @@ class Context:
         check(lib.mp_ctx_set_trace_variant(self._h, variant))
 
     def set_node_layout(self, layout):
-        """LAYOUT_DECODED (default: f32 child boxes / triangle edges written at upload) or LAYOUT_QUANTISED (reference records)."""
+        """LAYOUT_AUTO (default), LAYOUT_DECODED (f32 child boxes / triangle edges written at upload) or LAYOUT_QUANTISED (reference records)."""
         check(lib.mp_ctx_set_node_layout(self._h, layout))
 
     def sync(self):

@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libminipath_b200.so")
+LIB_PATH = os.environ.get("MINIPATH_B200_LIB") or os.path.join(_HERE, "libminipath_b200.so")  # env override: A/B builds of the same ABI
 
 MP_OK, MP_EINVAL, MP_ECUDA, MP_ENODEVICE, MP_EIO, MP_ESTATE, MP_ENOMEM = 0, -1, -2, -3, -4, -5, -6
 LINK_NULL = 0xFFFFFFF8
@@ -19,7 +19,7 @@ TRI_FLAT = 0x80000000
 MODE_MEGAKERNEL, MODE_WAVEFRONT = 0, 1
 ORDER_REFERENCE, ORDER_NEAR_FIRST = 0, 1
 TRACE_THREAD, TRACE_OCTET, TRACE_PERSIST, TRACE_HYBRID, TRACE_POOL, TRACE_HYBRID_POOL = 0, 1, 2, 3, 4, 5
-LAYOUT_QUANTISED, LAYOUT_DECODED = 0, 1
+LAYOUT_QUANTISED, LAYOUT_DECODED, LAYOUT_AUTO = 0, 1, 2
 
 
 class MpError(RuntimeError):

@@ -37,7 +37,7 @@ struct MpCtx {
     mpd::Scene scene{};
     mpd::SceneCM scene_cm{};
     uint32_t trace_variant = MP_TRACE_THREAD;
-    uint32_t layout = MP_LAYOUT_DECODED;  // requested node layout
+    uint32_t layout = MP_LAYOUT_AUTO;     // requested node layout
     bool decoded_ok = false;              // the decoded arrays exist and passed the min <= max check
     uint32_t* d_flags = nullptr;
     int sm_count = 148;
@@ -258,7 +258,7 @@ int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant) {
 
 int mp_ctx_set_node_layout(MpCtx* ctx, uint32_t layout) {
     if (!ctx) return fail(MP_EINVAL, "null context");
-    if (layout > MP_LAYOUT_DECODED) return fail(MP_EINVAL, "bad node layout %u", layout);
+    if (layout > MP_LAYOUT_AUTO) return fail(MP_EINVAL, "bad node layout %u", layout);
     ctx->layout = layout;
     return MP_OK;
 }
@@ -318,7 +318,8 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     const size_t s_pack = al((size_t)b->n_packets * sizeof(MpTrianglePacket)), s_pbox = al((size_t)b->n_packets * sizeof(MpBox));
     const size_t s_sh = al((size_t)b->n_packets * 8 * sizeof(MpTriShading)), s_v = al((size_t)b->n_vertices * sizeof(MpVertexShading));
     const size_t s_inner_w = al((size_t)b->n_inner * MPD_NODE_W * sizeof(float4)), s_pack_w = al((size_t)b->n_packets * MPD_PACK_W * sizeof(float4));
-    const size_t total = 2 * s_inner + s_ibox + 2 * s_pack + s_pbox + s_sh + s_v + s_inner_w + s_pack_w + 256;
+    const size_t s_inner_r = al((size_t)b->n_inner * 160), s_pack_r = al((size_t)b->n_packets * 192);
+    const size_t total = 2 * s_inner + s_ibox + 2 * s_pack + s_pbox + s_sh + s_v + s_inner_w + s_pack_w + s_inner_r + s_pack_r + 256;
     if (total > ctx->scene_blob_cap) {  // pooled contexts keep the allocation between renders
         if (ctx->d_scene_blob) CK(cudaFree(ctx->d_scene_blob));
         ctx->d_scene_blob = nullptr, ctx->scene_blob_cap = 0, ctx->has_scene = false;
@@ -376,6 +377,18 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
         ctx->launches++;
     }
     mpd::decode_packets_kernel<<<(unsigned)(((size_t)b->n_packets * 8 + 255) / 256), 256, 0, ctx->stream>>>(ctx->scene, b->n_packets, packets_w);
+    ctx->launches++;
+    // quantised records for 256-bit gathers
+    uint4* inner_rec = (uint4*)p;
+    p += s_inner_r;
+    uint4* packets_rec = (uint4*)p;
+    p += s_pack_r;
+    ctx->scene.inner_rec = inner_rec, ctx->scene.packets_rec = packets_rec;
+    if (b->n_inner) {
+        mpd::build_inner_records_kernel<<<(unsigned)(((size_t)b->n_inner * 10 + 255) / 256), 256, 0, ctx->stream>>>(ctx->scene, b->n_inner, inner_rec);
+        ctx->launches++;
+    }
+    mpd::build_packet_records_kernel<<<(unsigned)(((size_t)b->n_packets * 12 + 255) / 256), 256, 0, ctx->stream>>>(ctx->scene, b->n_packets, packets_rec);
     ctx->launches++;
     uint32_t h_flags = 0;
     CK(cudaMemcpyAsync(&h_flags, ctx->d_flags, sizeof h_flags, cudaMemcpyDeviceToHost, ctx->stream));

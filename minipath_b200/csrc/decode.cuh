@@ -56,4 +56,21 @@ __global__ void __launch_bounds__(256) decode_packets_kernel(Scene sc, uint32_t 
     o[6 * 8 + c] = e2.x, o[7 * 8 + c] = e2.y, o[8 * 8 + c] = e2.z;
 }
 
+// Quantised records (trace.cuh: inner_rec / packets_rec): the reference rows, the links and the enclosing box interleaved into one
+// 32-byte-aligned record per node / packet so that a lane's gather is 5 (6) 256-bit loads.  One thread per 16-byte word.
+__global__ void __launch_bounds__(256) build_inner_records_kernel(Scene sc, uint32_t n_inner, uint4* __restrict__ out) {
+    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = gid / 10;
+    const uint32_t w = (uint32_t)(gid % 10);
+    if (i >= n_inner) return;
+    out[gid] = w < 8 ? sc.inner[8 * i + w] : reinterpret_cast<const uint4*>(sc.inner_box)[2 * i + (w - 8)];
+}
+__global__ void __launch_bounds__(256) build_packet_records_kernel(Scene sc, uint32_t n_packets, uint4* __restrict__ out) {
+    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t p = gid / 12;
+    const uint32_t w = (uint32_t)(gid % 12);
+    if (p >= n_packets) return;
+    out[gid] = w < 9 ? sc.packets[9 * p + w] : (w < 11 ? reinterpret_cast<const uint4*>(sc.packet_box)[2 * p + (w - 9)] : make_uint4(0u, 0u, 0u, 0u));
+}
+
 }  // namespace mpd

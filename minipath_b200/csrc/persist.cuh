@@ -12,53 +12,6 @@
 
 namespace mpd {
 
-// One inner node for one ray, either layout; `stk` is a stack view (LocalStack, or the pool's interleaved stacks).
-template <int LAYOUT, int ORDER, bool NANPATH, class S>
-__device__ __forceinline__ void persist_inner(const Scene& sc, const Ray& r, const RaySel& sel, uint32_t index, float max_t, const S& stk, int& sp) {
-    if (LAYOUT == MP_LAYOUT_DECODED) {
-        inner_decoded<ORDER, NANPATH>(sc, r, sel, index, max_t, stk, sp);
-        return;
-    }
-    const float4 b0 = __ldg(sc.inner_box + 2 * (size_t)index), b1 = __ldg(sc.inner_box + 2 * (size_t)index + 1);
-    const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
-    const uint4* n = sc.inner + 8 * (size_t)index;
-    uint4 q[6];
-#pragma unroll
-    for (int k = 0; k < 6; ++k) q[k] = __ldg(n + k);
-    const uint4 la = __ldg(n + 6), lb = __ldg(n + 7);
-    const uint32_t links[8] = {la.x, la.y, la.z, la.w, lb.x, lb.y, lb.z, lb.w};
-    const int base = sp;
-#pragma unroll
-    for (int lane = 0; lane < 8; ++lane) {
-        if (links[lane] == MP_LINK_NULL) continue;  // discarded when popped (:49); skipping is neutral
-        float t1;
-        if (child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1)) push_child<ORDER>(stk, base, sp, links[lane], t1);
-    }
-}
-
-// One packet of a leaf for one ray, either layout (ray_bvh_intersection.rs:104-141).
-template <int LAYOUT>
-__device__ __forceinline__ void persist_packet(const Scene& sc, const Ray& r, uint32_t pidx, float max_t, Hit& local) {
-    if (LAYOUT == MP_LAYOUT_DECODED) {
-        packet_decoded(sc, r, pidx, max_t, local);
-        return;
-    }
-    const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)pidx), b1 = __ldg(sc.packet_box + 2 * (size_t)pidx + 1);
-    const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
-    const uint4* pk = sc.packets + 9 * (size_t)pidx;
-    uint4 q[9];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) q[k] = __ldg(pk + k);
-#pragma unroll
-    for (int lane = 0; lane < 8; ++lane) {
-        float t, u, v;
-        if (tri_lane(q, lane, bmin, bsize, r, max_t, t, u, v) && t < local.t) {
-            local.t = t, local.u = u, local.v = v;
-            local.tri = pidx * 8u + (uint32_t)lane;
-        }
-    }
-}
-
 // fetch(i, r) loads ray i completely (o, d, inv); emit(i, best) stores its result.
 template <int LAYOUT, int ORDER, bool COUNT, class Fetch, class Emit>
 __device__ __forceinline__ void persist_run(const Scene& sc, uint32_t n, uint32_t first, uint32_t stride, bool any_hit, Fetch fetch, Emit emit,
@@ -112,15 +65,17 @@ __device__ __forceinline__ void persist_run(const Scene& sc, uint32_t n, uint32_
         if (__popc(m_in) >= __popc(m_lf)) {
             if (kind == 1) {
                 if (COUNT) tc.vis.inner++;
+                StackSink<ORDER, LocalStack> sink{LocalStack{stk}, sp, sp};
                 if (nanpath)
-                    persist_inner<LAYOUT, ORDER, true>(sc, r, sel, p_index, best.t, LocalStack{stk}, sp);
+                    visit_inner<LAYOUT, true>(sc, r, sel, p_index, best.t, sink);
                 else
-                    persist_inner<LAYOUT, ORDER, false>(sc, r, sel, p_index, best.t, LocalStack{stk}, sp);
+                    visit_inner<LAYOUT, false>(sc, r, sel, p_index, best.t, sink);
+                sp = sink.sp;
                 kind = 0;
             }
         } else if (kind == 2) {
             // ---- one packet of the leaf (ray_bvh_intersection.rs:104-141) ----
-            persist_packet<LAYOUT>(sc, r, p_index, lf_max_t, lf_local);
+            visit_packet<LAYOUT>(sc, r, p_index, lf_max_t, lf_local);
             ++p_index;
             if (--lf_rem == 0) {
                 kind = 0;

@@ -18,11 +18,21 @@
 
 namespace mpd {
 
+#ifndef POOL_W
 #define POOL_W 96       // ray slots per warp
+#endif
 #define POOL_RING 128   // ring capacity (power of two >= POOL_W)
-#define POOL_COLS 22    // 4-byte state columns per slot
+#define POOL_COLS 21    // 4-byte state columns per slot
 #define POOL_WARPS 4    // warps per block
-#define POOL_SMEM_PER_WARP (POOL_COLS * POOL_W * 4 + 3 * POOL_RING)
+#ifndef POOL_MIN_BLOCKS
+#define POOL_MIN_BLOCKS 5  // resident blocks per SM the register allocation aims at; measured: 6 (80 regs) and 8 (64 regs, 64-ray pools) are 3-15 % slower
+#endif
+#ifndef POOL_SS
+#define POOL_SS 0       // entries of every ray's stack kept in shared memory (power of two, 0 = none); the rest lives in the global scratch.
+                        // Measured on the stand-in (8 spp, ms per frame): 0 -> 79.4, 2 -> 85.8, 4 -> 86.7: the ring bookkeeping in the unrolled
+                        // child loop and the lost occupancy cost more than the L1 requests it saves, so it is off.
+#endif
+#define POOL_SMEM_PER_WARP (POOL_COLS * POOL_W * 4 + 3 * POOL_RING + POOL_SS * POOL_W * 8)
 
 struct PoolWarp {  // shared-memory view of one warp's pool
     float* col;          // [POOL_COLS][POOL_W]
@@ -32,13 +42,59 @@ struct PoolWarp {  // shared-memory view of one warp's pool
 };
 // columns
 enum { PC_OX, PC_OY, PC_OZ, PC_DX, PC_DY, PC_DZ, PC_IX, PC_IY, PC_IZ, PC_BT, PC_BU, PC_BV, PC_BTRI, PC_SP, PC_RID, PC_PIDX, PC_REM,
-       PC_LMAX, PC_LT, PC_LU, PC_LV, PC_LTRI };
+       PC_LT, PC_LU, PC_LV, PC_LTRI };
 
-// The stacks of a warp's 96 rays are interleaved entry-major in the global scratch ([entry][slot]): lanes working on rays at a
-// similar depth touch neighbouring 8-byte words instead of 96 separate regions.
-struct PoolStack {
-    uint2* p;  // entry 0 of this slot
-    __device__ __forceinline__ uint2& at(int i) const { return p[(size_t)i * POOL_W]; }
+// Per-ray traversal stack.  Profiling the first pool kernel showed three quarters of its global L1 requests were stack pushes and
+// pops (profiles/r1c_wf_trace_pool_records.txt): every lane touches its own line.  With SHORT the newest POOL_SS entries of a
+// ray's stack live in shared memory as a ring ([entry % POOL_SS][slot], 8-byte words, neighbouring slots in neighbouring banks)
+// and only entries pushed deeper than that spill to the global scratch ([entry][slot]); `lo` is the first entry held in the ring.
+// NEAR_FIRST needs random access for its insertion sort and keeps the whole stack in the scratch (SHORT = false).
+template <bool SHORT>
+struct PStack {
+    uint2* ring;   // shared memory, this ray's column
+    uint2* spill;  // global scratch, this ray's column
+    int sp, lo;
+    __device__ __forceinline__ uint2& at(int i) const { return spill[(size_t)i * POOL_W]; }  // !SHORT only
+    __device__ __forceinline__ void push(uint2 e) {
+        if (SHORT) {
+            if (sp - lo == POOL_SS) {  // ring full: the oldest entry goes to the scratch
+                spill[(size_t)lo * POOL_W] = ring[(lo & (POOL_SS - 1)) * POOL_W];
+                ++lo;
+            }
+            ring[(sp & (POOL_SS - 1)) * POOL_W] = e;
+            ++sp;
+        } else {
+            spill[(size_t)sp * POOL_W] = e;
+            ++sp;
+        }
+    }
+    __device__ __forceinline__ uint2 pop() {  // sp > 0
+        --sp;
+        if (SHORT) {
+            if (sp >= lo) return ring[(sp & (POOL_SS - 1)) * POOL_W];
+            lo = sp;  // ring empty: take the entry back from the scratch
+        }
+        return spill[(size_t)sp * POOL_W];
+    }
+    __device__ __forceinline__ void clear() { sp = 0, lo = 0; }
+    __device__ __forceinline__ uint32_t pack() const { return SHORT ? ((uint32_t)sp | (uint32_t)lo << 16) : (uint32_t)sp; }
+    __device__ __forceinline__ void unpack(uint32_t v) {
+        sp = SHORT ? (int)(v & 0xffffu) : (int)v;
+        lo = SHORT ? (int)(v >> 16) : 0;
+    }
+};
+
+// DeferSink (trace.cuh) on a PStack: every hit child but the last is pushed, the last is handed to pool_advance.
+template <class S>
+struct PoolDeferSink {
+    S& stk;
+    uint2 top;
+    bool has;
+    __device__ __forceinline__ void hit(uint32_t link, float t1) {
+        if (has) stk.push(top);
+        top = make_uint2(link, __float_as_uint(t1));
+        has = true;
+    }
 };
 
 struct PoolQueues {  // warp-uniform ring cursors
@@ -53,15 +109,22 @@ __device__ __forceinline__ void pool_push(const PoolWarp& pw, PoolQueues& qs, in
     qs.tail[q] += __popc(m);
 }
 
-// Pop the ray's next surviving entry and file the slot; `active` lanes own `slot` with current (sp, best_t).
-template <bool COUNT, class Emit>
-__device__ __forceinline__ void pool_advance(const PoolWarp& pw, PoolQueues& qs, bool active, uint32_t slot, const PoolStack stk, int sp, float best_t,
-                                             Emit emit, ThreadCounts& tc) {
+// Pop the ray's next surviving entry and file the slot; `active` lanes own `slot` with stack `stk` and current best_t.  `has_top`:
+// the entry the inner phase kept in registers instead of pushing it (PoolDeferSink), or the root of a fresh ray — it is the top of
+// the stack and needs no `t1 > best.t` test (t1 <= t2 <= max_t = best.t; the root carries -inf).
+template <bool COUNT, class S, class Emit>
+__device__ __forceinline__ void pool_advance(const PoolWarp& pw, PoolQueues& qs, bool active, uint32_t slot, S& stk, float best_t, Emit emit,
+                                             ThreadCounts& tc, bool has_top = false, uint2 top = make_uint2(0u, 0u)) {
     uint32_t kind = 0;  // 0 finished, 1 inner, 2 leaf
     if (active) {
-        while (sp > 0) {
-            const uint2 e = stk.at(--sp);
-            if (__uint_as_float(e.y) > best_t) continue;  // ray_bvh_intersection.rs:40
+        while (has_top || stk.sp > 0) {
+            uint2 e;
+            if (has_top) {
+                e = top, has_top = false;
+            } else {
+                e = stk.pop();
+                if (__uint_as_float(e.y) > best_t) continue;  // ray_bvh_intersection.rs:40
+            }
             const uint32_t count = e.x & MP_LINK_COUNT_MASK;
             pw.u(PC_PIDX, slot) = e.x >> MP_LINK_COUNT_BITS;
             pw.u(PC_REM, slot) = count;
@@ -69,14 +132,13 @@ __device__ __forceinline__ void pool_advance(const PoolWarp& pw, PoolQueues& qs,
                 kind = 1;
             } else {
                 kind = 2;
-                pw.f(PC_LMAX, slot) = best_t;  // max_t is not updated inside the leaf
-                pw.f(PC_LT, slot) = MPD_INF;
+                pw.f(PC_LT, slot) = MPD_INF;  // max_t of the leaf is best.t, which does not change until the leaf is finished
                 pw.u(PC_LTRI, slot) = MP_NO_HIT;
                 if (COUNT) tc.vis.leaves++, tc.vis.packets += count;
             }
             break;
         }
-        pw.u(PC_SP, slot) = (uint32_t)sp;
+        pw.u(PC_SP, slot) = stk.pack();
         if (kind == 0)
             emit(pw.u(PC_RID, slot), Hit{pw.f(PC_BT, slot), pw.f(PC_BU, slot), pw.f(PC_BV, slot), pw.u(PC_BTRI, slot)});
     }
@@ -104,6 +166,9 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
     pw.col = reinterpret_cast<float*>(smem + (size_t)warp * POOL_SMEM_PER_WARP);
     pw.ring = smem + (size_t)warp * POOL_SMEM_PER_WARP + POOL_COLS * POOL_W * 4;
     uint2* const wstacks = scratch + ((size_t)blockIdx.x * POOL_WARPS + warp) * POOL_W * stack_cap;
+    uint2* const wring = reinterpret_cast<uint2*>(smem + (size_t)warp * POOL_SMEM_PER_WARP + POOL_COLS * POOL_W * 4 + 3 * POOL_RING);
+    constexpr bool SHORT = ORDER == MP_ORDER_REFERENCE && POOL_SS > 0;
+    using Stack = PStack<SHORT>;
     PoolQueues qs{};
     for (uint32_t s = lane; s < POOL_W; s += 32) pw.ring[2 * POOL_RING + s] = (unsigned char)s;  // every slot starts free
     qs.tail[2] = POOL_W;
@@ -131,11 +196,11 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
                 pw.f(PC_IX, slot) = r.inv.x, pw.f(PC_IY, slot) = r.inv.y, pw.f(PC_IZ, slot) = r.inv.z;
                 pw.f(PC_BT, slot) = MPD_FLT_MAX, pw.f(PC_BU, slot) = 0.0f, pw.f(PC_BV, slot) = 0.0f, pw.u(PC_BTRI, slot) = MP_NO_HIT;
                 pw.u(PC_RID, slot) = base + lane;
-                wstacks[slot] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
                 tc.rays++;
             }
             qs.head[2] += got;
-            pool_advance<COUNT>(pw, qs, act, slot, PoolStack{wstacks + slot}, 1, MPD_FLT_MAX, emit, tc);
+            Stack stk{wring + slot, wstacks + slot, 0, 0};
+            pool_advance<COUNT>(pw, qs, act, slot, stk, MPD_FLT_MAX, emit, tc, true, make_uint2(sc.root, __float_as_uint(MPD_NINF)));
             __syncwarp();
             continue;
         }
@@ -146,54 +211,64 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
             const uint32_t take = n_in < 32 ? n_in : 32;
             const bool act = lane < take;
             uint32_t slot = 0;
-            int sp = 0;
             float bt = 0.0f;
-            PoolStack stk{wstacks};
+            Stack stk{wring, wstacks, 0, 0};
+            bool has_top = false;
+            uint2 top = make_uint2(0u, 0u);
             if (act) {
                 slot = pw.ring[0 * POOL_RING + ((qs.head[0] + lane) & (POOL_RING - 1))];
-                stk.p = wstacks + slot;
+                stk.ring = wring + slot, stk.spill = wstacks + slot;
+                stk.unpack(pw.u(PC_SP, slot));
                 const Ray r = pool_load_ray(pw, slot);
                 bt = pw.f(PC_BT, slot);
-                sp = (int)pw.u(PC_SP, slot);
                 const uint32_t node = pw.u(PC_PIDX, slot);
                 if (COUNT) tc.vis.inner++;
-                if (ray_needs_nanpath(r)) {
-                    persist_inner<LAYOUT, ORDER, true>(sc, r, RaySel{}, node, bt, stk, sp);
+                const bool nanpath = ray_needs_nanpath(r);
+                RaySel sel{};
+                if (LAYOUT == MP_LAYOUT_DECODED && !nanpath) sel = ray_sel(r);
+                if (ORDER == MP_ORDER_REFERENCE) {
+                    PoolDeferSink<Stack> sink{stk, make_uint2(0u, 0u), false};
+                    if (nanpath)
+                        visit_inner<LAYOUT, true>(sc, r, sel, node, bt, sink);
+                    else
+                        visit_inner<LAYOUT, false>(sc, r, sel, node, bt, sink);
+                    has_top = sink.has, top = sink.top;
                 } else {
-                    RaySel sel{};
-                    if (LAYOUT == MP_LAYOUT_DECODED) sel = ray_sel(r);
-                    persist_inner<LAYOUT, ORDER, false>(sc, r, sel, node, bt, stk, sp);
+                    StackSink<ORDER, Stack> sink{stk, stk.sp, stk.sp};
+                    if (nanpath)
+                        visit_inner<LAYOUT, true>(sc, r, sel, node, bt, sink);
+                    else
+                        visit_inner<LAYOUT, false>(sc, r, sel, node, bt, sink);
+                    stk.sp = sink.sp;
                 }
             }
             qs.head[0] += take;
-            pool_advance<COUNT>(pw, qs, act, slot, stk, sp, bt, emit, tc);
+            pool_advance<COUNT>(pw, qs, act, slot, stk, bt, emit, tc, has_top, top);
         } else {
             // ---- 32 triangle packets, one per ray (ray_bvh_intersection.rs:104-141) ----
             const uint32_t take = n_lf < 32 ? n_lf : 32;
             const bool act = lane < take;
             uint32_t slot = 0;
-            int sp = 0;
             float bt = 0.0f;
-            PoolStack stk{wstacks};
+            Stack stk{wring, wstacks, 0, 0};
             bool done = false;  // the leaf's last packet has been tested
             if (act) {
                 slot = pw.ring[1 * POOL_RING + ((qs.head[1] + lane) & (POOL_RING - 1))];
-                stk.p = wstacks + slot;
                 const Ray r = pool_load_ray(pw, slot);
                 uint32_t pidx = pw.u(PC_PIDX, slot), rem = pw.u(PC_REM, slot);
-                const float max_t = pw.f(PC_LMAX, slot);
+                bt = pw.f(PC_BT, slot);  // = the leaf's max_t: best.t is not updated inside the leaf (:106-107)
                 Hit local{pw.f(PC_LT, slot), pw.f(PC_LU, slot), pw.f(PC_LV, slot), pw.u(PC_LTRI, slot)};
-                persist_packet<LAYOUT>(sc, r, pidx, max_t, local);
+                visit_packet<LAYOUT>(sc, r, pidx, bt, local);
                 ++pidx, --rem;
                 pw.u(PC_PIDX, slot) = pidx, pw.u(PC_REM, slot) = rem;
-                sp = (int)pw.u(PC_SP, slot);
-                bt = pw.f(PC_BT, slot);
                 if (rem == 0) {
                     done = true;
+                    stk.ring = wring + slot, stk.spill = wstacks + slot;
+                    stk.unpack(pw.u(PC_SP, slot));
                     if (local.t < bt) {  // :59
                         bt = local.t;
                         pw.f(PC_BT, slot) = local.t, pw.f(PC_BU, slot) = local.u, pw.f(PC_BV, slot) = local.v, pw.u(PC_BTRI, slot) = local.tri;
-                        if (any_hit) sp = 0;
+                        if (any_hit) stk.clear();
                     }
                 } else {
                     pw.f(PC_LT, slot) = local.t, pw.f(PC_LU, slot) = local.u, pw.f(PC_LV, slot) = local.v, pw.u(PC_LTRI, slot) = local.tri;
@@ -201,7 +276,7 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
             }
             qs.head[1] += take;
             pool_push(pw, qs, 1, act && !done, slot);  // more packets of the same leaf: back into the packet queue
-            pool_advance<COUNT>(pw, qs, act && done, slot, stk, sp, bt, emit, tc);
+            pool_advance<COUNT>(pw, qs, act && done, slot, stk, bt, emit, tc);
         }
         __syncwarp();
     }
@@ -210,7 +285,7 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
 // ---- kernels: 128 threads = 4 pools per block, persistent grid ----
 
 template <int LAYOUT, int ORDER, bool COUNT>
-__global__ void __launch_bounds__(128) trace_rays_pool_kernel(Scene sc, const float* __restrict__ rays, uint32_t n, uint4* __restrict__ hits,
+__global__ void __launch_bounds__(128, POOL_MIN_BLOCKS) trace_rays_pool_kernel(Scene sc, const float* __restrict__ rays, uint32_t n, uint4* __restrict__ hits,
                                                               DevCounters* dc, uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];
     ThreadCounts tc{};
@@ -227,7 +302,7 @@ __global__ void __launch_bounds__(128) trace_rays_pool_kernel(Scene sc, const fl
 }
 
 template <int LAYOUT, int ORDER, bool COUNT>
-__global__ void __launch_bounds__(128) wf_trace_pool_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
+__global__ void __launch_bounds__(128, POOL_MIN_BLOCKS) wf_trace_pool_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
                                                             const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
                                                             uint4* __restrict__ hit, DevCounters* dc, uint32_t* claim, uint2* scratch,
                                                             uint32_t stack_cap) {
@@ -244,7 +319,7 @@ __global__ void __launch_bounds__(128) wf_trace_pool_kernel(Scene sc, const uint
 }
 
 template <int LAYOUT, int ORDER, bool COUNT>
-__global__ void __launch_bounds__(128) wf_shadow_pool_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
+__global__ void __launch_bounds__(128, POOL_MIN_BLOCKS) wf_shadow_pool_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
                                                              const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, DevCounters* dc,
                                                              uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];

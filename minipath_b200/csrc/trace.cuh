@@ -25,6 +25,8 @@ struct Scene {
     const float4* __restrict__ packet_box;
     const uint4* __restrict__ tri_shading;
     const float4* __restrict__ vertices;
+    const uint4* __restrict__ inner_rec;   // quantised node records: 6 bound rows, 2 link rows, box (min, size) = 160 B = 5 x LDG.256
+    const uint4* __restrict__ packets_rec; // quantised packet records: 9 rows, leaf box, pad = 192 B = 6 x LDG.256
     const float4* __restrict__ inner_w;    // decoded nodes (MP_LAYOUT_DECODED), MPD_NODE_W float4 each
     const float4* __restrict__ packets_w;  // decoded packets, MPD_PACK_W float4 each
     uint32_t root;
@@ -107,6 +109,16 @@ __device__ __forceinline__ bool tri_lane(const uint4 (&q)[9], int lane, const F3
 #define MPD_NODE_W 16
 #define MPD_PACK_W 18
 
+// 256-bit read-only load (LDG.E.256, sm_100+): a divergent gather costs one L1 wavefront per lane and INSTRUCTION whatever its
+// width (profiles/r1b_ubench_l1_patterns.txt: 10 x LDG.128 = 9.3 clk per node and SM, 5 x LDG.256 = 4.9), so the quantised
+// records are read 32 bytes at a time.
+__device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) {
+    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+        : "l"(p));
+}
+__device__ __forceinline__ float4 as_f4(const uint4& v) { return make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w)); }
+
 // A ray whose inverse direction is finite and non-NaN crosses the planes of a child box in a known order: (b - o) * inv is
 // monotonic in b, so min(lo, hi) is the plane on the side the ray comes from.  Decoded nodes keep min <= max per axis
 // (checked by decode_scene_kernel), hence the near / far rows can be picked per RAY instead of per child with 6 min/max.
@@ -136,27 +148,75 @@ struct LocalStack {
     __device__ __forceinline__ uint2& at(int i) const { return p[i]; }
 };
 
+// Where the hit children of a node go.  StackSink pushes every one (lanes ascending, so lane 7 pops first, :161; NEAR_FIRST keeps
+// the node's entries sorted far → near).  The pool kernel has its own sink (pool.cuh: PoolDeferSink) that keeps the LAST hit child
+// in registers instead of pushing it: that entry would be popped next and always survives `t1 > best.t` (:40) because
+// t1 <= t2 <= max_t = best.t, so handing it over directly saves a stack store and a load per inner node, same visiting order.
 template <int ORDER, class S>
-__device__ __forceinline__ void push_child(const S& stk, int base, int& sp, uint32_t link, float t1) {
-    if (ORDER == MP_ORDER_NEAR_FIRST) {
-        // keep this node's entries sorted far → near (ties: lower lane nearer the top)
-        int pos = sp;
-        while (pos > base && __uint_as_float(stk.at(pos - 1).y) <= t1) {
-            stk.at(pos) = stk.at(pos - 1);
-            --pos;
+struct StackSink {
+    S stk;
+    int base, sp;
+    __device__ __forceinline__ void hit(uint32_t link, float t1) {
+        if (ORDER == MP_ORDER_NEAR_FIRST) {
+            int pos = sp;  // ties: lower lane nearer the top
+            while (pos > base && __uint_as_float(stk.at(pos - 1).y) <= t1) {
+                stk.at(pos) = stk.at(pos - 1);
+                --pos;
+            }
+            stk.at(pos) = make_uint2(link, __float_as_uint(t1));
+            ++sp;
+        } else {
+            stk.at(sp++) = make_uint2(link, __float_as_uint(t1));
         }
-        stk.at(pos) = make_uint2(link, __float_as_uint(t1));
-        ++sp;
-    } else {
-        stk.at(sp++) = make_uint2(link, __float_as_uint(t1));  // lane order: lane 7 pops first (:161)
+    }
+};
+// InnerNode::intersect on a quantised node record (ray_bvh_intersection.rs:149-162).
+template <bool NANPATH, class Sink>
+__device__ __forceinline__ void inner_quantised(const Scene& sc, const Ray& r, uint32_t index, float max_t, Sink& sink) {
+    const uint4* n = sc.inner_rec + 10 * (size_t)index;
+    uint4 q[6], la, lb, b0, b1;
+    ldg256(n + 0, q[0], q[1]);
+    ldg256(n + 2, q[2], q[3]);
+    ldg256(n + 4, q[4], q[5]);
+    ldg256(n + 6, la, lb);
+    ldg256(n + 8, b0, b1);
+    const F3 bmin = f3(__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b0.z));
+    const F3 bsize = f3(__uint_as_float(b1.x), __uint_as_float(b1.y), __uint_as_float(b1.z));
+    const uint32_t links[8] = {la.x, la.y, la.z, la.w, lb.x, lb.y, lb.z, lb.w};
+#pragma unroll
+    for (int lane = 0; lane < 8; ++lane) {
+        if (links[lane] == MP_LINK_NULL) continue;  // all-zero bounds, discarded when popped (:49); skipping is neutral
+        float t1;
+        if (child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1)) sink.hit(links[lane], t1);
+    }
+}
+
+// One quantised packet record: RelativeTriangle8::decompress + Triangle<WorldPoint8>::intersect (ray_bvh_intersection.rs:104-141).
+__device__ __forceinline__ void packet_quantised(const Scene& sc, const Ray& r, uint32_t pidx, float max_t, Hit& local) {
+    const uint4* pk = sc.packets_rec + 12 * (size_t)pidx;
+    uint4 q[9], b0, b1, pad;
+    ldg256(pk + 0, q[0], q[1]);
+    ldg256(pk + 2, q[2], q[3]);
+    ldg256(pk + 4, q[4], q[5]);
+    ldg256(pk + 6, q[6], q[7]);
+    ldg256(pk + 8, q[8], b0);
+    ldg256(pk + 10, b1, pad);
+    const F3 bmin = f3(__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b0.z));
+    const F3 bsize = f3(__uint_as_float(b1.x), __uint_as_float(b1.y), __uint_as_float(b1.z));
+#pragma unroll
+    for (int lane = 0; lane < 8; ++lane) {
+        float t, u, v;
+        if (tri_lane(q, lane, bmin, bsize, r, max_t, t, u, v) && t < local.t) {
+            local.t = t, local.u = u, local.v = v;
+            local.tri = pidx * 8u + (uint32_t)lane;
+        }
     }
 }
 
 // InnerNode::intersect on a decoded node (ray_bvh_intersection.rs:149-162).
-template <int ORDER, bool NANPATH, class S>
-__device__ __forceinline__ void inner_decoded(const Scene& sc, const Ray& r, const RaySel& sel, uint32_t index, float max_t, const S& stk, int& sp) {
+template <bool NANPATH, class Sink>
+__device__ __forceinline__ void inner_decoded(const Scene& sc, const Ray& r, const RaySel& sel, uint32_t index, float max_t, Sink& sink) {
     const float4* n = sc.inner_w + MPD_NODE_W * (size_t)index;
-    const int base = sp;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {  // children 4h .. 4h+3
         const uint4 lk = __ldg(reinterpret_cast<const uint4*>(n + 12 + h));
@@ -179,7 +239,7 @@ __device__ __forceinline__ void inner_decoded(const Scene& sc, const Ray& r, con
                 const float cmaxx = maxps(lox, hix), cmaxy = maxps(loy, hiy), cmaxz = maxps(loz, hiz);
                 const float t1 = maxps(maxps(cminx, 0.0f), maxps(cminy, cminz));
                 const float t2 = minps(minps(cmaxx, max_t), minps(cmaxy, cmaxz));
-                if (t1 <= t2) push_child<ORDER>(stk, base, sp, comp(lk, k), t1);
+                if (t1 <= t2) sink.hit(comp(lk, k), t1);
             }
         } else {
             const float4 ax = __ldg(n + sel.nx + h), ay = __ldg(n + sel.ny + h), az = __ldg(n + sel.nz + h);
@@ -191,7 +251,7 @@ __device__ __forceinline__ void inner_decoded(const Scene& sc, const Ray& r, con
                 const float hiy = __fmul_rn(__fsub_rn(comp(by, k), r.o.y), r.inv.y), hiz = __fmul_rn(__fsub_rn(comp(bz, k), r.o.z), r.inv.z);
                 const float t1 = fmaxf(fmaxf(lox, loy), fmaxf(loz, 0.0f));    // FMNMX3 + FMNMX
                 const float t2 = fminf(fminf(hix, hiy), fminf(hiz, max_t));
-                if (t1 <= t2) push_child<ORDER>(stk, base, sp, comp(lk, k), t1);  // NULL children: t1 = +inf, t2 = -inf
+                if (t1 <= t2) sink.hit(comp(lk, k), t1);  // NULL children: t1 = +inf, t2 = -inf
             }
         }
     }
@@ -226,68 +286,46 @@ __device__ __forceinline__ void packet_decoded(const Scene& sc, const Ray& r, ui
     }
 }
 
+// One inner node / one packet for one ray in either layout.
+template <int LAYOUT, bool NANPATH, class Sink>
+__device__ __forceinline__ void visit_inner(const Scene& sc, const Ray& r, const RaySel& sel, uint32_t index, float max_t, Sink& sink) {
+    if (LAYOUT == MP_LAYOUT_DECODED)
+        inner_decoded<NANPATH>(sc, r, sel, index, max_t, sink);
+    else
+        inner_quantised<NANPATH>(sc, r, index, max_t, sink);
+}
+template <int LAYOUT>
+__device__ __forceinline__ void visit_packet(const Scene& sc, const Ray& r, uint32_t pidx, float max_t, Hit& local) {
+    if (LAYOUT == MP_LAYOUT_DECODED)
+        packet_decoded(sc, r, pidx, max_t, local);
+    else
+        packet_quantised(sc, r, pidx, max_t, local);
+}
+
 template <int LAYOUT, int ORDER, bool COUNT, bool NANPATH>
 __device__ __forceinline__ Hit trace_impl(const Scene& sc, const Ray& r, bool any_hit, Visits& vis) {
     uint2 stk[MPD_STACK_MAX];  // (link, t1 bits)
-    int sp = 0;
-    stk[sp++] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
+    stk[0] = make_uint2(sc.root, __float_as_uint(MPD_NINF));
+    StackSink<ORDER, LocalStack> sink{LocalStack{stk}, 0, 1};
     Hit best{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
     RaySel sel{};
     if (LAYOUT == MP_LAYOUT_DECODED && !NANPATH) sel = ray_sel(r);
 
-    while (sp > 0) {
-        uint2 e = stk[--sp];
+    while (sink.sp > 0) {
+        const uint2 e = stk[--sink.sp];
         if (__uint_as_float(e.y) > best.t) continue;  // ray_bvh_intersection.rs:40
         const uint32_t count = e.x & MP_LINK_COUNT_MASK, index = e.x >> MP_LINK_COUNT_BITS;
         if (count == 0) {
             // ---- inner node (ray_bvh_intersection.rs:149-162) ----
             if (COUNT) vis.inner++;
-            if (LAYOUT == MP_LAYOUT_DECODED) {
-                inner_decoded<ORDER, NANPATH>(sc, r, sel, index, best.t, LocalStack{stk}, sp);
-                continue;
-            }
-            const float4 b0 = __ldg(sc.inner_box + 2 * (size_t)index), b1 = __ldg(sc.inner_box + 2 * (size_t)index + 1);
-            const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
-            const uint4* n = sc.inner + 8 * (size_t)index;
-            uint4 q[6];
-#pragma unroll
-            for (int k = 0; k < 6; ++k) q[k] = __ldg(n + k);
-            const uint4 la = __ldg(n + 6), lb = __ldg(n + 7);
-            const uint32_t links[8] = {la.x, la.y, la.z, la.w, lb.x, lb.y, lb.z, lb.w};
-            const float max_t = best.t;
-            const int base = sp;
-#pragma unroll
-            for (int lane = 0; lane < 8; ++lane) {
-                // NULL children have all-zero bounds and are discarded when popped (:49); skipping them is neutral
-                if (links[lane] == MP_LINK_NULL) continue;
-                float t1;
-                if (child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1)) push_child<ORDER>(LocalStack{stk}, base, sp, links[lane], t1);
-            }
+            sink.base = sink.sp;
+            visit_inner<LAYOUT, NANPATH>(sc, r, sel, index, best.t, sink);
         } else {
             // ---- leaf: ≤7 packets of 8 triangles (ray_bvh_intersection.rs:104-141) ----
             if (COUNT) vis.leaves++, vis.packets += count;
             const float max_t = best.t;  // not updated inside the leaf
             Hit local{MPD_INF, 0.0f, 0.0f, MP_NO_HIT};
-            if (LAYOUT == MP_LAYOUT_DECODED) {
-                for (uint32_t j = 0; j < count; ++j) packet_decoded(sc, r, index + j, max_t, local);
-            } else {
-                const float4 b0 = __ldg(sc.packet_box + 2 * (size_t)index), b1 = __ldg(sc.packet_box + 2 * (size_t)index + 1);
-                const F3 bmin = f3(b0.x, b0.y, b0.z), bsize = f3(b1.x, b1.y, b1.z);
-                for (uint32_t j = 0; j < count; ++j) {
-                    const uint4* pk = sc.packets + 9 * (size_t)(index + j);
-                    uint4 q[9];
-#pragma unroll
-                    for (int k = 0; k < 9; ++k) q[k] = __ldg(pk + k);
-#pragma unroll
-                    for (int lane = 0; lane < 8; ++lane) {
-                        float t, u, v;
-                        if (tri_lane(q, lane, bmin, bsize, r, max_t, t, u, v) && t < local.t) {
-                            local.t = t, local.u = u, local.v = v;
-                            local.tri = (index + j) * 8u + (uint32_t)lane;
-                        }
-                    }
-                }
-            }
+            for (uint32_t j = 0; j < count; ++j) visit_packet<LAYOUT>(sc, r, index + j, max_t, local);
             if (local.t < best.t) {  // :59
                 best = local;
                 if (any_hit) break;
