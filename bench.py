@@ -69,6 +69,7 @@ WORKLOADS = {
     "cube-1080p": ("cube", 1920, 1080, 64, 5),         # configs[1], the cube half
     "teapot-bench": ("teapot", 2048, 1536, 10, 0),     # configs[0]: benches/render_teapot.rs:12-24 (reference shader)
     "atrium-1080p": ("atrium", 1920, 1080, 256, 5),    # configs[2] on the procedural Sponza stand-in (sponza.obj is absent)
+    "atrium-4k": ("atrium", 3840, 2160, 1024, 8),      # configs[3] on the stand-in: spp split over the GPUs, NCCL film reduce
 }
 
 

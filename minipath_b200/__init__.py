@@ -490,6 +490,10 @@ class Context:
         check(lib.mp_trace_rays(self._h, rays.ctypes.data, len(rays), order, hits.ctypes.data))
         return hits
 
+    def trace_rays_device(self, dev_rays, n, dev_hits, order=ORDER_REFERENCE):
+        """Object::intersect on rays already resident in HBM (device pointers, e.g. torch tensors); asynchronous."""
+        check(lib.mp_trace_rays_device(self._h, dev_rays, n, order, dev_hits))
+
     def generate_rays(self, tiles, params):
         arr, ptr, n = _tiles_arg(tiles)
         count = C.c_uint64()
