@@ -74,17 +74,20 @@ __device__ __forceinline__ uint32_t block_compact_slot(bool pred, uint32_t* coun
     return slot;
 }
 
-// Stage 1: CameraSampler::sample_ray (camera.rs:176-191) for sample `sample` of every pixel of the tile batch.
-__global__ void __launch_bounds__(128) wf_raygen_kernel(Camera cam, TileMap tm, uint32_t width, uint32_t sample, uint32_t seed_hash,
-                                                        float4* __restrict__ ray_o, float4* __restrict__ ray_d, uint4* __restrict__ meta,
-                                                        uint32_t* __restrict__ queue, uint32_t* count, DevCounters* dc) {
+// Stage 1: CameraSampler::sample_ray (camera.rs:176-191) for `n_samples` consecutive samples of every pixel of the tile batch.
+// Path slot = s * batch_threads + (thread index inside the batch): neighbouring slots are neighbouring pixels of one sample.
+__global__ void __launch_bounds__(128) wf_raygen_kernel(Camera cam, TileMap tm, uint32_t width, uint32_t sample_first, uint32_t n_samples,
+                                                        unsigned long long batch_threads, uint32_t seed_hash, float4* __restrict__ ray_o,
+                                                        float4* __restrict__ ray_d, uint4* __restrict__ meta, uint32_t* __restrict__ queue,
+                                                        uint32_t* count, DevCounters* dc) {
     const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t s = (uint32_t)(gid / batch_threads);
     uint32_t x = 0, y = 0, ti = 0;
-    const bool active = map_pixel(tm, gid, x, y, ti);
+    const bool active = s < n_samples && map_pixel(tm, gid % batch_threads, x, y, ti);
     ThreadCounts tc{};
     if (active) {
         const uint32_t pixel_index = y * width + x;
-        uint32_t rng = rng_init(pixel_index, sample, seed_hash);
+        uint32_t rng = rng_init(pixel_index, sample_first + s, seed_hash);
         const Ray r = sample_ray(cam, x, y, rng);
         ray_o[gid] = make_float4(r.o.x, r.o.y, r.o.z, 1.0f);
         ray_d[gid] = make_float4(r.d.x, r.d.y, r.d.z, 0.0f);
@@ -227,18 +230,21 @@ __global__ void __launch_bounds__(128) wf_shadow_kernel(Scene sc, const float4* 
     flush_counts(dc, tc, COUNT);
 }
 
-// Stage 4: film accumulation (worker.rs:42): film[pixel] += (L, L, L, alpha) for the pass's sample.
+// Stage 4: film accumulation (worker.rs:42): film[pixel] += (L, L, L, alpha), the pass's samples in sample order.
 __global__ void __launch_bounds__(128) wf_accumulate_kernel(TileMap tm, float4* __restrict__ film, const float4* __restrict__ ray_d,
-                                                            const uint4* __restrict__ meta) {
+                                                            const uint4* __restrict__ meta, uint32_t n_samples, unsigned long long batch_threads) {
     const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t x, y, ti;
     if (!map_pixel(tm, gid, x, y, ti)) return;
-    const uint4 m = meta[gid];
-    const float L = ray_d[gid].w;
-    const float alpha = (m.z & 0x80000000u) ? 1.0f : 0.0f;
-    float4 f = film[m.x];
-    f.x = __fadd_rn(f.x, L), f.y = __fadd_rn(f.y, L), f.z = __fadd_rn(f.z, L), f.w = __fadd_rn(f.w, alpha);
-    film[m.x] = f;
+    const uint32_t pixel = meta[gid].x;
+    float4 f = film[pixel];
+    for (uint32_t s = 0; s < n_samples; ++s) {
+        const unsigned long long slot = s * batch_threads + gid;
+        const float L = ray_d[slot].w;
+        const float alpha = (meta[slot].z & 0x80000000u) ? 1.0f : 0.0f;
+        f.x = __fadd_rn(f.x, L), f.y = __fadd_rn(f.y, L), f.z = __fadd_rn(f.z, L), f.w = __fadd_rn(f.w, alpha);
+    }
+    film[pixel] = f;
 }
 
 }  // namespace mpd
