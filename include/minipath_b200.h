@@ -329,6 +329,9 @@ int mp_progress_abort(MpRenderProgress* p);                             /* :161-
 int mp_progress_wait(MpRenderProgress* p);                              /* :169-173 */
 /* Copies the RGBA8 image (w*h*4) under the image lock (:175-177). */
 int mp_progress_image(MpRenderProgress* p, uint8_t* host_out, size_t cap);
+/* The image itself (pinned host memory, w*h*4 bytes, valid until mp_progress_free) — what `image()` hands out behind its
+ * Mutex (:175-177); tiles appear in it while the render runs, it is complete once mp_progress_wait has returned. */
+int mp_progress_image_ptr(MpRenderProgress* p, const uint8_t** out, size_t* out_bytes);
 int mp_progress_free(MpRenderProgress* p);
 
 /* Cross-process dynamic tile queue (the AtomicUsize of machinery.rs:43,205-209 shared by the ranks of one box). */

@@ -307,6 +307,18 @@ class Scene:
 # ---------------------------------------------------------------------------------------------------------
 # render() and RenderProgress (reference src/renderer/machinery.rs)
 # ---------------------------------------------------------------------------------------------------------
+class _ImageView(np.ndarray):
+    """ndarray view of the library-owned image that keeps its RenderProgress (the owner of the memory) alive."""
+
+    def __new__(cls, arr, owner):
+        obj = np.asarray(arr).view(cls)
+        obj._owner = owner
+        return obj
+
+    def __array_finalize__(self, obj):
+        self._owner = getattr(obj, "_owner", None)
+
+
 class RenderProgressSnapshot:
     def __init__(self, finished, total):
         self.finished, self.total = finished, total
@@ -340,12 +352,24 @@ class RenderProgress:
     def wait(self):
         check(lib.mp_progress_wait(self._h))
 
-    def image(self):
-        """RGBA8 image as (H, W, 4) uint8, copied under the image lock (machinery.rs:175-177)."""
+    def image(self, copy=None):
+        """RGBA8 image as (H, W, 4) uint8 (machinery.rs:175-177).  The reference hands out the image itself behind its lock; so does
+        this once the render is finished: a read-only view of the library's (pinned) image that keeps this RenderProgress alive.
+        While workers are still writing tiles (or with copy=True) a snapshot copied under the image lock is returned instead."""
         w, h = self._settings.resolution
-        img = np.empty((h, w, 4), np.uint8)
-        check(lib.mp_progress_image(self._h, img.ctypes.data, img.nbytes))
-        return img
+        if copy is None:
+            copy = not self.is_finished()
+        if copy:
+            img = np.empty((h, w, 4), np.uint8)
+            check(lib.mp_progress_image(self._h, img.ctypes.data, img.nbytes))
+            return img
+        ptr, nbytes = C.c_void_p(), C.c_size_t()
+        check(lib.mp_progress_image_ptr(self._h, C.byref(ptr), C.byref(nbytes)))
+        buf = (C.c_uint8 * nbytes.value).from_address(ptr.value)
+        view = np.frombuffer(buf, dtype=np.uint8).reshape(h, w, 4)
+        view.flags.writeable = False
+        self._views = getattr(self, "_views", 0) + 1
+        return _ImageView(view, self)
 
     def __del__(self):
         if getattr(self, "_h", None):
@@ -356,14 +380,15 @@ class RenderProgress:
 def render(scene, camera, settings, started_tile_callback=None, finished_tile_callback=None, devices=None):
     """minipath::render (machinery.rs:20-123): returns immediately; tiles render on one worker thread per GPU."""
     def _started(_user, tile):
-        if started_tile_callback:
-            started_tile_callback(ScreenBlock((tile.min_x, tile.min_y), (tile.max_x, tile.max_y)))
+        started_tile_callback(ScreenBlock((tile.min_x, tile.min_y), (tile.max_x, tile.max_y)))
 
     def _finished(_user, tile, snap):
-        if finished_tile_callback:
-            finished_tile_callback(ScreenBlock((tile.min_x, tile.min_y), (tile.max_x, tile.max_y)), RenderProgressSnapshot(snap.finished, snap.total))
+        finished_tile_callback(ScreenBlock((tile.min_x, tile.min_y), (tile.max_x, tile.max_y)), RenderProgressSnapshot(snap.finished, snap.total))
 
-    cb0, cb1 = _ffi.STARTED_FN(_started), _ffi.FINISHED_FN(_finished)
+    # no callback given → NULL function pointer: a ctypes trampoline per tile costs a GIL round trip from the worker thread
+    # (768 tiles x 2 callbacks were 6 ms of a 9 ms frame)
+    cb0 = _ffi.STARTED_FN(_started) if started_tile_callback else _ffi.STARTED_FN()
+    cb1 = _ffi.FINISHED_FN(_finished) if finished_tile_callback else _ffi.FINISHED_FN()
     raw = settings._raw()
     dev_arr, n_dev = None, 0
     if devices:

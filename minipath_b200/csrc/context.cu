@@ -339,31 +339,18 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     ctx->scene.packet_box = (const float4*)up(b->packet_box, (size_t)b->n_packets * sizeof(MpBox), s_pbox);
     ctx->scene.tri_shading = (const uint4*)up(b->tri_shading, (size_t)b->n_packets * 8 * sizeof(MpTriShading), s_sh);
     ctx->scene.vertices = (const float4*)up(b->vertices, (size_t)b->n_vertices * sizeof(MpVertexShading), s_v);
-    // child-major copies for the octet kernels (octet.cuh): one 16-byte record per child / per triangle
-    std::vector<uint32_t> cm_inner((size_t)b->n_inner * 32), cm_pack((size_t)b->n_packets * 36);
-    for (size_t i = 0; i < b->n_inner; ++i) {
-        const MpInnerNode& nd = b->inner[i];
-        for (int k = 0; k < 8; ++k) {
-            uint32_t* o = &cm_inner[i * 32 + k * 4];
-            o[0] = nd.bounds[0][k] | (uint32_t)nd.bounds[1][k] << 16;
-            o[1] = nd.bounds[2][k] | (uint32_t)nd.bounds[3][k] << 16;
-            o[2] = nd.bounds[4][k] | (uint32_t)nd.bounds[5][k] << 16;
-            o[3] = nd.links[k];
-        }
+    // child-major copies for the octet kernels (octet.cuh), written on the device
+    uint4* inner_cm = (uint4*)p;
+    p += s_inner;
+    uint4* packets_cm = (uint4*)p;
+    p += s_pack;
+    ctx->scene_cm.inner_cm = inner_cm, ctx->scene_cm.packets_cm = packets_cm;
+    if (b->n_inner) {
+        mpd::build_inner_cm_kernel<<<(unsigned)(((size_t)b->n_inner * 8 + 255) / 256), 256, 0, ctx->stream>>>(ctx->scene, b->n_inner, inner_cm);
+        ctx->launches++;
     }
-    for (size_t i = 0; i < b->n_packets; ++i) {
-        const MpTrianglePacket& pk = b->packets[i];
-        for (int k = 0; k < 8; ++k) {
-            uint32_t* o = &cm_pack[i * 36 + k * 4];
-            o[0] = pk.v[0][0][k] | (uint32_t)pk.v[0][1][k] << 16;
-            o[1] = pk.v[0][2][k] | (uint32_t)pk.v[1][0][k] << 16;
-            o[2] = pk.v[1][1][k] | (uint32_t)pk.v[1][2][k] << 16;
-            o[3] = pk.v[2][0][k] | (uint32_t)pk.v[2][1][k] << 16;
-        }
-        for (int w = 0; w < 4; ++w) cm_pack[i * 36 + 32 + w] = pk.v[2][2][2 * w] | (uint32_t)pk.v[2][2][2 * w + 1] << 16;
-    }
-    ctx->scene_cm.inner_cm = (const uint4*)up(cm_inner.data(), cm_inner.size() * 4, s_inner);
-    ctx->scene_cm.packets_cm = (const uint4*)up(cm_pack.data(), cm_pack.size() * 4, s_pack);
+    mpd::build_packets_cm_kernel<<<(unsigned)(((size_t)b->n_packets * 9 + 255) / 256), 256, 0, ctx->stream>>>(ctx->scene, b->n_packets, packets_cm);
+    ctx->launches++;
     // decoded layout (trace.cuh): written on the device from the arrays just uploaded
     float4* inner_w = (float4*)p;
     p += s_inner_w;

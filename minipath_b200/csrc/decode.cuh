@@ -73,4 +73,28 @@ __global__ void __launch_bounds__(256) build_packet_records_kernel(Scene sc, uin
     out[gid] = w < 9 ? sc.packets[9 * p + w] : (w < 11 ? reinterpret_cast<const uint4*>(sc.packet_box)[2 * p + (w - 9)] : make_uint4(0u, 0u, 0u, 0u));
 }
 
+// Child-major copies for the octet kernels (octet.cuh): one 16-byte record per child / per triangle, + the row of eight v2.z.
+__global__ void __launch_bounds__(256) build_inner_cm_kernel(Scene sc, uint32_t n_inner, uint4* __restrict__ out) {
+    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = gid >> 3;
+    const uint32_t k = (uint32_t)(gid & 7u);
+    if (i >= n_inner) return;
+    const uint16_t* b = reinterpret_cast<const uint16_t*>(sc.inner + 8 * i);  // bounds[6][8]
+    const uint32_t link = reinterpret_cast<const uint32_t*>(sc.inner + 8 * i + 6)[k];
+    out[gid] = make_uint4(b[0 * 8 + k] | (uint32_t)b[1 * 8 + k] << 16, b[2 * 8 + k] | (uint32_t)b[3 * 8 + k] << 16,
+                          b[4 * 8 + k] | (uint32_t)b[5 * 8 + k] << 16, link);
+}
+__global__ void __launch_bounds__(256) build_packets_cm_kernel(Scene sc, uint32_t n_packets, uint4* __restrict__ out) {
+    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t p = gid / 9;
+    const uint32_t k = (uint32_t)(gid % 9);
+    if (p >= n_packets) return;
+    const uint16_t* v = reinterpret_cast<const uint16_t*>(sc.packets + 9 * p);  // v[vertex*3 + axis][lane]
+    if (k < 8)
+        out[gid] = make_uint4(v[0 * 8 + k] | (uint32_t)v[1 * 8 + k] << 16, v[2 * 8 + k] | (uint32_t)v[3 * 8 + k] << 16,
+                              v[4 * 8 + k] | (uint32_t)v[5 * 8 + k] << 16, v[6 * 8 + k] | (uint32_t)v[7 * 8 + k] << 16);
+    else
+        out[gid] = sc.packets[9 * p + 8];  // the eight v2.z as they are
+}
+
 }  // namespace mpd

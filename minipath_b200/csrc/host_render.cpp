@@ -4,6 +4,8 @@
 // shared image under its mutex (machinery.rs:78-89), firing the reference's two callbacks from the worker thread.
 #include <atomic>
 #include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <random>
@@ -14,13 +16,45 @@
 
 using namespace mp;
 
+// Pinned image buffers are expensive to create (cudaMallocHost of a 1080p image ~ 1 ms) and renders repeat: keep a few.
+static std::mutex g_img_mutex;
+static std::vector<std::pair<uint8_t*, size_t>> g_img_pool;
+static uint8_t* image_acquire(size_t bytes) {
+    uint8_t* ptr = nullptr;
+    {
+        std::lock_guard<std::mutex> g(g_img_mutex);
+        for (size_t i = 0; i < g_img_pool.size(); ++i)
+            if (g_img_pool[i].second == bytes) {
+                ptr = g_img_pool[i].first;
+                g_img_pool.erase(g_img_pool.begin() + i);
+                break;
+            }
+    }
+    if (!ptr && mp_host_alloc_pinned(bytes, (void**)&ptr) != MP_OK) return nullptr;
+    memset(ptr, 0, bytes);  // RgbaImage::new (machinery.rs:34)
+    return ptr;
+}
+static void image_release(uint8_t* ptr, size_t bytes) {
+    if (!ptr) return;
+    {
+        std::lock_guard<std::mutex> g(g_img_mutex);
+        if (g_img_pool.size() < 4) {
+            g_img_pool.emplace_back(ptr, bytes);
+            return;
+        }
+    }
+    mp_host_free_pinned(ptr);
+}
+
 struct MpRenderProgress {
+    ~MpRenderProgress() { image_release(image, image_bytes); }
     // RenderState (machinery.rs:191-203)
     MpRenderSettings settings{};
     MpCameraSampler sampler{};
     const MpFlatBvh* scene = nullptr;
     std::mutex image_mutex;
-    std::vector<uint8_t> image;  // RGBA8, w*h*4
+    uint8_t* image = nullptr;  // RGBA8, w*h*4, pinned (taken from / returned to the process-wide pool below)
+    size_t image_bytes = 0;
     std::vector<MpTile> tile_ordering;
     std::atomic<size_t> next_tile_index{0};
     std::chrono::steady_clock::time_point start_time;
@@ -88,12 +122,24 @@ static void worker_main(MpRenderProgress* p, int device) {
     const MpRenderSettings& s = p->settings;
     const size_t total = p->tile_ordering.size();
     MpCtx* ctx = nullptr;
+    const bool timing = getenv("MINIPATH_B200_TIMING") != nullptr;  // developer aid: where a render's host time goes
+    auto t_mark = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[mp_render dev %d] %-14s %.3f ms\n", device, what, std::chrono::duration<double, std::milli>(now - t_mark).count());
+        t_mark = now;
+    };
+    lap("thread start");
     int rc = mp_ctx_pool_acquire(device, &ctx);
     if (!rc) rc = mp_ctx_set_trace_variant(ctx, p->trace_variant);
+    lap("ctx acquire");
     if (!rc) rc = mp_scene_upload(ctx, p->scene);
+    lap("scene upload");
     if (!rc) rc = mp_camera_set(ctx, &p->sampler);  // camera.build_sampler(settings.resolution) (machinery.rs:65)
     if (!rc) rc = mp_film_create(ctx, s.resolution_x, s.resolution_y);
     if (!rc) rc = mp_tiles_upload(ctx, p->tile_ordering.data(), (uint32_t)total, s.tile_size);
+    lap("film+tiles");
     MpRenderParams params{};
     params.sample_count = s.sample_count;
     params.sample_base = 0;
@@ -112,6 +158,21 @@ static void worker_main(MpRenderProgress* p, int device) {
         const size_t n = std::min(p->batch, total - first);
         if (p->started)
             for (size_t i = 0; i < n; ++i) p->started(p->user, p->tile_ordering[first + i]);
+        if (first == 0 && n == total) {
+            // the whole frame in one batch (default for one device): resolve straight into the pinned image, no tile staging
+            rc = mp_render_tile_range(ctx, 0, (uint32_t)n, &params);
+            lap("launch");
+            if (!rc) {
+                std::lock_guard<std::mutex> g(p->image_mutex);
+                rc = mp_film_resolve_rgba8(ctx, s.sample_count, p->image);
+            }
+            lap("render+resolve");
+            if (!rc && p->finished) {
+                const MpProgressSnapshot snap{total, total};
+                for (size_t i = 0; i < n; ++i) p->finished(p->user, p->tile_ordering[i], snap);
+            }
+            continue;
+        }
         rc = finish_batch(p, ctx, pending[slot], slot);  // this slot's previous batch (two batches back) leaves first
         if (!rc) rc = mp_render_tile_range(ctx, (uint32_t)first, (uint32_t)n, &params);  // worker.render_tile (machinery.rs:77)
         if (!rc) rc = mp_film_resolve_tiles_begin(ctx, (uint32_t)first, (uint32_t)n, s.tile_size, s.sample_count, slot);
@@ -125,6 +186,7 @@ static void worker_main(MpRenderProgress* p, int device) {
     if (ctx) {
         if (rc) mp_ctx_destroy(ctx); else mp_ctx_pool_release(ctx);
     }
+    lap("release");
     {
         auto elapsed = std::chrono::steady_clock::now() - p->start_time;  // machinery.rs:107-113
         std::lock_guard<std::mutex> g(p->end_mutex);
@@ -168,7 +230,12 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
         delete p;
         return rc;
     }
-    p->image.assign((size_t)settings->resolution_x * settings->resolution_y * 4, 0);  // RgbaImage::new (machinery.rs:34)
+    p->image_bytes = (size_t)settings->resolution_x * settings->resolution_y * 4;
+    p->image = image_acquire(p->image_bytes);
+    if (!p->image) {
+        delete p;
+        return fail(MP_ENOMEM, "pinned image allocation failed");
+    }
     size_t n_tiles = 0;
     mp_tile_ordering(0, 0, settings->resolution_x, settings->resolution_y, settings->tile_size, 0, nullptr, 0, &n_tiles);
     p->tile_ordering.resize(n_tiles);
@@ -239,8 +306,14 @@ int mp_progress_wait(MpRenderProgress* p) {  // machinery.rs:169-173
 int mp_progress_image(MpRenderProgress* p, uint8_t* host_out, size_t cap) {  // machinery.rs:175-177
     if (!p || !host_out) return fail(MP_EINVAL, "null argument");
     std::lock_guard<std::mutex> g(p->image_mutex);
-    if (cap < p->image.size()) return fail(MP_EINVAL, "image buffer too small: %zu < %zu", cap, p->image.size());
-    memcpy(host_out, p->image.data(), p->image.size());
+    if (cap < p->image_bytes) return fail(MP_EINVAL, "image buffer too small: %zu < %zu", cap, p->image_bytes);
+    memcpy(host_out, p->image, p->image_bytes);
+    return MP_OK;
+}
+int mp_progress_image_ptr(MpRenderProgress* p, const uint8_t** out, size_t* out_bytes) {  // the &RgbaImage behind the lock, no copy
+    if (!p || !out) return fail(MP_EINVAL, "null argument");
+    *out = p->image;
+    if (out_bytes) *out_bytes = p->image_bytes;
     return MP_OK;
 }
 int mp_progress_free(MpRenderProgress* p) {
