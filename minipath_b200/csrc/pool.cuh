@@ -51,6 +51,7 @@ enum { PC_OX, PC_OY, PC_OZ, PC_DX, PC_DY, PC_DZ, PC_IX, PC_IY, PC_IZ, PC_BT, PC_
 // NEAR_FIRST needs random access for its insertion sort and keeps the whole stack in the scratch (SHORT = false).
 template <bool SHORT>
 struct PStack {
+    static constexpr bool kShort = SHORT;
     uint2* ring;   // shared memory, this ray's column
     uint2* spill;  // global scratch, this ray's column
     int sp, lo;
@@ -121,9 +122,24 @@ __device__ __forceinline__ void pool_advance(const PoolWarp& pw, PoolQueues& qs,
             uint2 e;
             if (has_top) {
                 e = top, has_top = false;
-            } else {
+            } else if (S::kShort) {
                 e = stk.pop();
                 if (__uint_as_float(e.y) > best_t) continue;  // ray_bvh_intersection.rs:40
+            } else {
+                // Two entries per iteration, both loads in flight before either is tested: a run of culled entries is otherwise a
+                // chain of dependent L2 round trips (13 % of the kernel's stall samples sat on this test, profiles/r1d_wf_pool_32Mpaths.txt).
+                const int i = stk.sp - 1;
+                const uint2 a = stk.at(i);
+                const uint2 b = stk.at(i > 0 ? i - 1 : 0);
+                stk.sp = i;
+                if (!(__uint_as_float(a.y) > best_t)) {  // ray_bvh_intersection.rs:40
+                    e = a;
+                } else if (i > 0 && !(__uint_as_float(b.y) > best_t)) {
+                    e = b, stk.sp = i - 1;
+                } else {
+                    stk.sp = i > 0 ? i - 1 : 0;
+                    continue;
+                }
             }
             const uint32_t count = e.x & MP_LINK_COUNT_MASK;
             pw.u(PC_PIDX, slot) = e.x >> MP_LINK_COUNT_BITS;
