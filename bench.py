@@ -339,7 +339,7 @@ def run_b200(args, rank, local, world):
     value = rays_job / (ms_per_step * 1e-3) / 1e6
 
     res = dict(ctx=ctx, bvh=bvh, cam=cam, w=w, h=h, spp=spp, bounces=bounces, tiles=tiles, cnt=cnt, ab=ab, mode_name=mode_name,
-               ms_per_step=ms_per_step, value=value, samples_per_s=samples_job / (ms_per_step * 1e-3), clocks=clocks,
+               ms_per_step=ms_per_step, value=value, world=world, samples_per_s=samples_job / (ms_per_step * 1e-3), clocks=clocks,
                launches=launches, rays_job=rays_job, stream=stream, torch=torch, dist=dist, modes=modes, variants=variants, order=order, barrier=barrier)
     return res
 
@@ -425,8 +425,18 @@ def roofline(args, res):
         out = {"bound": "fp32", "achieved": flops / secs / 1e12, "peak": fp32, "unit": "TFLOP/s", "frac": t_fp32 / secs}
     else:
         out = {"bound": mem_bound[0], "achieved": bytes_ / secs / 1e9, "peak": mem_bound[2], "unit": "GB/s", "frac": mem_bound[1] / secs}
+    traffic, traffic_note = None, "no ncu capture recorded for this workload/pipeline (scripts/ncu_traffic.py)"
+    try:  # DRAM bytes of the traversal launches of one step, from an ncu capture of this very command line (profiles/traffic.json)
+        rec = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{args.workload}/{res['mode_name']}")
+        if rec and args.spp == 0 and args.bounces < 0 and res["world"] == 1:
+            traffic = rec["dram_bytes_per_step"]
+            traffic_note = f"dram__bytes_read.sum + dram__bytes_write.sum over the {rec['launches']} traversal launches of one step ({rec['source']})"
+        elif rec:
+            traffic_note = "recorded for the workload's own spp/bounces on 1 GPU only"
+    except Exception:
+        pass
     out.update({
-        "traffic": None,
+        "traffic": traffic, "traffic_note": traffic_note, "algorithmic_bytes_per_step": bytes_,
         "kernel": {"megakernel": "render_mega_kernel", "wavefront-octet": "wf_trace_octet_kernel+wf_shadow_octet_kernel",
                    "wavefront-thread": "wf_trace_kernel+wf_shadow_kernel",
                    "wavefront-persist": "wf_trace_persist_kernel+wf_shadow_persist_kernel",

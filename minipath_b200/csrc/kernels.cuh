@@ -65,6 +65,20 @@ __device__ __forceinline__ bool map_pixel(const TileMap& tm, unsigned long long 
     return x < t.max_x && y < t.max_y;
 }
 
+// Same mapping for launches whose thread index fits 32 bits (every wavefront batch): no 64-bit division.
+__device__ __forceinline__ bool map_pixel32(const TileMap& tm, uint32_t gid, uint32_t& x, uint32_t& y, uint32_t& tile_index) {
+    const uint32_t ti = gid / tm.threads_per_tile;
+    if (ti >= tm.n_tiles) return false;
+    const uint32_t rem = gid - ti * tm.threads_per_tile;
+    const uint32_t mt = rem >> 5, l = rem & 31u;
+    const MpTile t = tm.tiles[ti];
+    const uint32_t my = mt / tm.mt_x;
+    x = t.min_x + (mt - my * tm.mt_x) * 8u + (l & 7u);
+    y = t.min_y + my * 4u + (l >> 3);
+    tile_index = ti;
+    return x < t.max_x && y < t.max_y;
+}
+
 // Worker::render_sample (worker.rs:51-65) for max_bounces == 0; extension integrator otherwise.
 template <int LAYOUT, int ORDER, bool COUNT>
 __device__ __forceinline__ float4 render_sample(const Scene& sc, const Camera& cam, uint32_t px, uint32_t py, uint32_t pixel_index,

@@ -9,6 +9,7 @@
 namespace mpd {
 
 #define WF_MAX_DEPTH 64
+#define WF_STAGE_THREADS 512  // block size of the ray-gen and shade stages (one queue atomic per block)
 
 struct WavefrontBuffers {
     size_t cap = 0;               // path slots
@@ -52,21 +53,23 @@ inline cudaError_t wavefront_reserve(WavefrontBuffers& w, size_t cap) {
 // Warp ballot gives the intra-warp rank, a prefix sum over the warp totals in shared memory gives the intra-block
 // offset, and one atomicAdd per block reserves the range.
 __device__ __forceinline__ uint32_t block_compact_slot(bool pred, uint32_t* counter) {
-    __shared__ uint32_t warp_base[4];
+    // any block size up to 1024 (a multiple of 32): the 512-thread stages issue a quarter of the single-address atomics of 128-thread blocks
+    __shared__ uint32_t warp_base[32];
     __shared__ uint32_t block_base;
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     const uint32_t ballot = __ballot_sync(0xffffffffu, pred);
     if (lane == 0) warp_base[warp] = __popc(ballot);
     __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t total = 0;
+    if (warp == 0) {
+        const uint32_t c = lane < n_warps ? warp_base[lane] : 0u;
+        uint32_t incl = c;  // inclusive scan of the warp totals
 #pragma unroll
-        for (int w = 0; w < 4; ++w) {
-            const uint32_t c = warp_base[w];
-            warp_base[w] = total;
-            total += c;
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= (uint32_t)d) incl += v;
         }
-        block_base = total ? atomicAdd(counter, total) : 0u;
+        if (lane < n_warps) warp_base[lane] = incl - c;
+        if (lane == 31) block_base = incl ? atomicAdd(counter, incl) : 0u;
     }
     __syncthreads();
     const uint32_t slot = block_base + warp_base[warp] + __popc(ballot & ((1u << lane) - 1u));
@@ -76,14 +79,15 @@ __device__ __forceinline__ uint32_t block_compact_slot(bool pred, uint32_t* coun
 
 // Stage 1: CameraSampler::sample_ray (camera.rs:176-191) for `n_samples` consecutive samples of every pixel of the tile batch.
 // Path slot = s * batch_threads + (thread index inside the batch): neighbouring slots are neighbouring pixels of one sample.
-__global__ void __launch_bounds__(128) wf_raygen_kernel(Camera cam, TileMap tm, uint32_t width, uint32_t sample_first, uint32_t n_samples,
+__global__ void __launch_bounds__(WF_STAGE_THREADS) wf_raygen_kernel(Camera cam, TileMap tm, uint32_t width, uint32_t sample_first, uint32_t n_samples,
                                                         unsigned long long batch_threads, uint32_t seed_hash, float4* __restrict__ ray_o,
                                                         float4* __restrict__ ray_d, uint4* __restrict__ meta, uint32_t* __restrict__ queue,
                                                         uint32_t* count, DevCounters* dc) {
-    const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t s = (uint32_t)(gid / batch_threads);
+    // grid = (blocks of the batch, samples of the pass): blockIdx.y is the sample, no division to find it
+    const uint32_t s = blockIdx.y, g = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned long long gid = (unsigned long long)s * batch_threads + g;
     uint32_t x = 0, y = 0, ti = 0;
-    const bool active = s < n_samples && map_pixel(tm, gid % batch_threads, x, y, ti);
+    const bool active = s < n_samples && g < batch_threads && map_pixel32(tm, g, x, y, ti);
     ThreadCounts tc{};
     if (active) {
         const uint32_t pixel_index = y * width + x;
@@ -131,7 +135,7 @@ __global__ void __launch_bounds__(128) wf_trace_kernel(Scene sc, const uint32_t*
 
 // Stage 3: hit finalisation + shading + light/BSDF sampling; survivors are compacted into the next queue and
 // shadow rays into the shadow queue.
-__global__ void __launch_bounds__(128) wf_shade_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
+__global__ void __launch_bounds__(WF_STAGE_THREADS) wf_shade_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
                                                        uint32_t* __restrict__ next_queue, uint32_t* next_count,
                                                        float4* __restrict__ sh_o, uint32_t* __restrict__ sh_path, uint32_t* sh_count,
                                                        float4* __restrict__ ray_o, float4* __restrict__ ray_d, const uint4* __restrict__ hit,
@@ -233,9 +237,9 @@ __global__ void __launch_bounds__(128) wf_shadow_kernel(Scene sc, const float4* 
 // Stage 4: film accumulation (worker.rs:42): film[pixel] += (L, L, L, alpha), the pass's samples in sample order.
 __global__ void __launch_bounds__(128) wf_accumulate_kernel(TileMap tm, float4* __restrict__ film, const float4* __restrict__ ray_d,
                                                             const uint4* __restrict__ meta, uint32_t n_samples, unsigned long long batch_threads) {
-    const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t x, y, ti;
-    if (!map_pixel(tm, gid, x, y, ti)) return;
+    if (gid >= batch_threads || !map_pixel32(tm, gid, x, y, ti)) return;
     const uint32_t pixel = meta[gid].x;
     float4 f = film[pixel];
     for (uint32_t s = 0; s < n_samples; ++s) {
