@@ -429,7 +429,7 @@ def roofline(args, res):
     try:  # DRAM bytes of the traversal launches of one step, from an ncu capture of this very command line (profiles/traffic.json)
         rec = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{args.workload}/{res['mode_name']}")
         if rec and args.spp == 0 and args.bounces < 0 and res["world"] == 1:
-            traffic = rec["dram_bytes_per_step"]
+            traffic = rec["dram_bytes_per_step"] * (res["spp"] / rec["spp"] if "spp" in rec else 1.0)  # captured at a reduced spp: linear in spp
             traffic_note = f"dram__bytes_read.sum + dram__bytes_write.sum over the {rec['launches']} traversal launches of one step ({rec['source']})"
         elif rec:
             traffic_note = "recorded for the workload's own spp/bounces on 1 GPU only"
