@@ -17,10 +17,12 @@ $(CS)/host_camera.o: $(CS)/host_camera.cpp $(CS)/host_common.h include/minipath_
 	$(CXX) $(HOST_FLAGS) -c $< -o $@
 $(CS)/host_render.o: $(CS)/host_render.cpp $(CS)/host_common.h include/minipath_b200.h
 	$(CXX) $(HOST_FLAGS) -c $< -o $@
+$(CS)/host_image.o: $(CS)/host_image.cpp $(CS)/host_common.h include/minipath_b200.h
+	$(CXX) $(HOST_FLAGS) -c $< -o $@
 $(CS)/context.o: $(CS)/context.cu $(CS)/context_render.inc $(CS)/context_probes.inc $(CS)/probes.cuh $(CS)/octet.cuh $(CS)/persist.cuh $(CS)/pool.cuh $(CS)/decode.cuh $(CS)/kernels.cuh $(CS)/wavefront.cuh $(CS)/trace.cuh $(CS)/device_math.cuh include/minipath_b200.h
 	$(NVCC) $(NVCC_FLAGS) -c $< -o $@ 2> $(CS)/ptxas.log || (cat $(CS)/ptxas.log; false)
 
-$(LIB): $(CS)/host_bvh.o $(CS)/host_camera.o $(CS)/host_render.o $(CS)/context.o
+$(LIB): $(CS)/host_bvh.o $(CS)/host_camera.o $(CS)/host_render.o $(CS)/host_image.o $(CS)/context.o
 	$(NVCC) -shared -o $@ $^ -lpthread -lrt -cudart static
 
 $(ORACLE): oracle/oracle.cpp oracle/oracle_trace.inc oracle/oracle_render.inc oracle/oracle.h include/minipath_b200.h

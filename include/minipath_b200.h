@@ -334,6 +334,11 @@ int mp_progress_image(MpRenderProgress* p, uint8_t* host_out, size_t cap);
 int mp_progress_image_ptr(MpRenderProgress* p, const uint8_t** out, size_t* out_bytes);
 int mp_progress_free(MpRenderProgress* p);
 
+/* Image output (the reference never saves its image, src/cli.rs:44-46): 8-bit RGBA PNG with stored deflate
+ * blocks, or binary PPM without alpha.  Headless — bytes to a file. */
+int mp_image_write_png(const char* path, const uint8_t* rgba, uint32_t width, uint32_t height);
+int mp_image_write_ppm(const char* path, const uint8_t* rgba, uint32_t width, uint32_t height);
+
 /* Cross-process dynamic tile queue (the AtomicUsize of machinery.rs:43,205-209 shared by the ranks of one box). */
 typedef struct MpTileQueue MpTileQueue;
 int mp_tileq_open(const char* name, int create, MpTileQueue** out);

@@ -398,6 +398,16 @@ def render(scene, camera, settings, started_tile_callback=None, finished_tile_ca
     return RenderProgress(handle, settings, (cb0, cb1, scene, dev_arr))
 
 
+def save_image(path, rgba):
+    """Write an (H, W, 4) uint8 image as PNG (or PPM when the path ends in .ppm).  The reference has no image writer."""
+    img = np.ascontiguousarray(rgba, dtype=np.uint8)
+    h, w, c = img.shape
+    if c != 4:
+        raise ValueError("expected an RGBA image")
+    fn = lib.mp_image_write_ppm if str(path).lower().endswith(".ppm") else lib.mp_image_write_png
+    check(fn(str(path).encode(), img.ctypes.data, w, h))
+
+
 # ---------------------------------------------------------------------------------------------------------
 # device context (one per GPU): the seam under Worker::render_tile / Object::intersect
 # ---------------------------------------------------------------------------------------------------------

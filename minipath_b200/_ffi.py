@@ -233,6 +233,8 @@ PROTOTYPES = {
     "mp_progress_wait": (_i, [_vp]),
     "mp_progress_image": (_i, [_vp, _vp, C.c_size_t]),
     "mp_progress_image_ptr": (_i, [_vp, _P(_vp), _P(C.c_size_t)]),
+    "mp_image_write_png": (_i, [C.c_char_p, _vp, _u32, _u32]),
+    "mp_image_write_ppm": (_i, [C.c_char_p, _vp, _u32, _u32]),
     "mp_progress_free": (_i, [_vp]),
     "mp_tileq_open": (_i, [C.c_char_p, _i, _P(_vp)]),
     "mp_tileq_reset": (_i, [_vp]),
