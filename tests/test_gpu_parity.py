@@ -286,3 +286,61 @@ def test_equal_spp_per_pixel_statistics(gpu_ctx, oracle, teapot, teapot_camera):
     assert np.array_equal(mg[flat], mc[flat])
     z = np.abs(mg[~flat] - mc[~flat]) / se[~flat]
     assert (z > 4).mean() <= 3e-3, f"{(z > 4).sum()} of {z.size} pixels beyond |z| = 4"
+
+
+# ---- edge cases: ragged and empty inputs, error behaviour ------------------------------------------------------------------
+
+@pytest.mark.parametrize("mode", [mp.MODE_MEGAKERNEL, mp.MODE_WAVEFRONT])
+def test_ragged_tiles_and_odd_sizes(gpu_ctx, oracle, teapot, teapot_camera, mode):
+    """Resolution not a multiple of the tile size, tile size not a multiple of the 8x4 micro-tile, a 1-pixel-wide last column:
+    tiles are clipped at the right / bottom edge like ScreenBlock::tile_ordering does (screen_block.rs:46-60); film bit-exact."""
+    for (w, h, ts) in ((67, 45, 16), (33, 9, 13), (1, 1, 64), (130, 3, 7)):
+        s = _setup(gpu_ctx, teapot, teapot_camera, w, h)
+        st = mp.RenderSettings(ts, 3, (w, h), max_bounces=2, seed=11, mode=mode)
+        tiles = mp.full_screen_tiles(w, h, ts, seed=2)
+        assert sum(int(t["max_x"] - t["min_x"]) * int(t["max_y"] - t["min_y"]) for t in tiles) == w * h
+        gpu_ctx.render_tiles(tiles, st.params())
+        film_cpu, _, _ = oracle.render_tiles(teapot, s, w, h, tiles, st.params())
+        assert np.array_equal(_bits(gpu_ctx.read_film()), _bits(film_cpu)), (w, h, ts)
+
+
+def test_empty_inputs_are_no_ops(gpu_ctx, teapot, teapot_camera):
+    """Zero tiles and zero rays succeed and change nothing (the reference's loops simply do not run)."""
+    w, h = 64, 48
+    _setup(gpu_ctx, teapot, teapot_camera, w, h)
+    st = mp.RenderSettings(32, 2, (w, h), seed=1)
+    gpu_ctx.render_tiles(mp.full_screen_tiles(w, h, 32)[:0], st.params())
+    assert not gpu_ctx.read_film().any()
+    assert len(gpu_ctx.trace_rays(np.zeros(0, mp.RAY_DTYPE))) == 0
+
+
+def test_error_behaviour(gpu_ctx, teapot, teapot_camera):
+    """Where the reference panics (NonZeroU32 sample_count, tiles outside the image) the C ABI returns MP_EINVAL / MP_ESTATE."""
+    w, h = 64, 48
+    _setup(gpu_ctx, teapot, teapot_camera, w, h)
+    tiles = mp.full_screen_tiles(w, h, 32)
+    with pytest.raises(mp.MpError):
+        gpu_ctx.render_tiles(tiles, mp.RenderSettings(32, 1, (w, h), seed=1).params(sample_count=0))
+    with pytest.raises(mp.MpError):
+        gpu_ctx.render_tiles(tiles, mp.RenderSettings(16, 1, (w, h), seed=1).params())  # tiles larger than tile_size
+    big = tiles.copy()
+    big["max_x"] += 64
+    with pytest.raises(mp.MpError):
+        gpu_ctx.render_tiles(big, mp.RenderSettings(128, 1, (w, h), seed=1).params())  # outside the film
+    fresh = mp.Context(0)
+    try:
+        with pytest.raises(mp.MpError):
+            fresh.render_tiles(tiles, mp.RenderSettings(32, 1, (w, h), seed=1).params())  # no scene / camera / film yet
+    finally:
+        fresh.close()
+
+
+def test_many_samples_span_several_passes(gpu_ctx, oracle, teapot, teapot_camera):
+    """A batch whose samples do not fit one wavefront pass (S < spp) accumulates in sample order across passes."""
+    w, h, spp = 512, 384, 200  # 196 608 pixel threads -> 170 samples per 32 M-path pass -> two passes
+    s = _setup(gpu_ctx, teapot, teapot_camera, w, h)
+    st = mp.RenderSettings(64, spp, (w, h), max_bounces=0, seed=4, mode=mp.MODE_WAVEFRONT)
+    tiles = mp.full_screen_tiles(w, h, 64, seed=1)
+    gpu_ctx.render_tiles(tiles, st.params())
+    film_cpu, _, _ = oracle.render_tiles(teapot, s, w, h, tiles, st.params())
+    assert np.array_equal(_bits(gpu_ctx.read_film()), _bits(film_cpu))
