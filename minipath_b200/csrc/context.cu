@@ -1,6 +1,7 @@
 // Device context and the C ABI around the kernels (include/minipath_b200.h).
 // nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -prec-div=true -prec-sqrt=true -lineinfo
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>

@@ -234,6 +234,93 @@ __global__ void __launch_bounds__(128) wf_shadow_kernel(Scene sc, const float4* 
     flush_counts(dc, tc, COUNT);
 }
 
+// Stages 1-3 of depth 0 in ONE kernel: camera ray → closest hit (thread per ray: camera rays are coherent) → shade, with the path
+// in registers.  As separate stages a camera path crosses HBM four times (ray written, read by the trace, hit written, everything
+// read again by the shade) although most camera rays of a sparse scene end right there (three quarters of the teapot's miss); fused,
+// a path writes its direction + radiance and its meta word once, and only the survivors write an origin and queue entries.
+// The memory left behind is exactly what wf_raygen + wf_trace + wf_shade at depth 0 leave (minus the hit record, which only the
+// shade stage of the same depth reads), so the later stages are unchanged.
+template <int LAYOUT, int ORDER, bool COUNT>
+__global__ void __launch_bounds__(128) wf_primary_kernel(Scene sc, Camera cam, TileMap tm, uint32_t width, uint32_t sample_first, uint32_t n_samples,
+                                                         unsigned long long batch_threads, uint32_t seed_hash, uint32_t max_bounces,
+                                                         float4* __restrict__ ray_o, float4* __restrict__ ray_d, uint4* __restrict__ meta,
+                                                         uint32_t* __restrict__ next_queue, uint32_t* next_count, float4* __restrict__ sh_o,
+                                                         uint32_t* __restrict__ sh_path, uint32_t* sh_count, DevCounters* dc) {
+    const uint32_t s = blockIdx.y, g = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned long long gid = (unsigned long long)s * batch_threads + g;
+    uint32_t x = 0, y = 0, ti = 0;
+    const bool active = s < n_samples && g < batch_threads && map_pixel32(tm, g, x, y, ti);
+    ThreadCounts tc{};
+    bool survive = false, shadow = false;
+    float4 so = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (active) {
+        const uint32_t pixel_index = y * width + x;
+        uint32_t rng = rng_init(pixel_index, sample_first + s, seed_hash);
+        const Ray r = sample_ray(cam, x, y, rng);
+        tc.camera_rays = 1, tc.rays = 1;
+        const Hit h = trace<LAYOUT, ORDER, COUNT>(sc, r, false, tc.vis);
+        // ---- wf_shade_kernel at depth 0 (T = 1, L = 0) ----
+        float T = 1.0f, L = 0.0f;
+        uint4 m = make_uint4(pixel_index, rng, 0u, 0u);
+        float4 out_d = make_float4(r.d.x, r.d.y, r.d.z, 0.0f);
+        if (max_bounces == 0) {  // the reference shader (worker.rs:57-64)
+            if (h.tri != MP_NO_HIT) {
+                L = fabsf(dotn(r.d, shading_normal(sc, h)));
+                m.z |= 0x80000000u;
+            }
+            out_d.w = L;
+        } else if (h.tri == MP_NO_HIT) {
+            out_d.w = __fadd_rn(L, __fmul_rn(T, EXT_ENV));
+        } else {
+            m.z |= 0x80000000u;  // depth 0: alpha = primary hit
+            if (0u != max_bounces) {
+                F3 nrm = shading_normal(sc, h);
+                if (dotn(r.d, nrm) > 0.0f) nrm = neg(nrm);
+                const F3 origin = (r.o + r.d * h.t) + nrm * sc.eps;
+                T = __fmul_rn(T, EXT_ALBEDO);
+                const float c = dotn(nrm, f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
+                if (c > 0.0f) {
+                    shadow = true;
+                    so = make_float4(origin.x, origin.y, origin.z, __fmul_rn(__fmul_rn(T, EXT_SUN_E), c));
+                }
+                survive = true;  // Russian roulette starts at depth EXT_RR_START >= 1
+                if (0u >= EXT_RR_START) {
+                    const float q = u01(m.y);
+                    if (q >= T)
+                        survive = false;
+                    else
+                        T = __fdiv_rn(T, T);
+                }
+                if (survive) {
+                    float dx, dy;
+                    unit_disc(m.y, dx, dy);
+                    const float z = __fsqrt_rn(fmaxf(0.0f, __fsub_rn(1.0f, __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)))));
+                    const float sign = copysignf(1.0f, nrm.z);
+                    const float a = __fdiv_rn(-1.0f, __fadd_rn(sign, nrm.z));
+                    const float b = __fmul_rn(__fmul_rn(nrm.x, nrm.y), a);
+                    const F3 t1 = f3(__fadd_rn(1.0f, __fmul_rn(__fmul_rn(sign, __fmul_rn(nrm.x, nrm.x)), a)), __fmul_rn(sign, b), __fmul_rn(-sign, nrm.x));
+                    const F3 t2 = f3(b, __fadd_rn(sign, __fmul_rn(__fmul_rn(nrm.y, nrm.y), a)), -nrm.y);
+                    const F3 dir = (t1 * dx + t2 * dy) + nrm * z;
+                    const Ray nr = ray_new(origin, dir);
+                    ray_o[gid] = make_float4(nr.o.x, nr.o.y, nr.o.z, T);
+                    out_d = make_float4(nr.d.x, nr.d.y, nr.d.z, L);
+                    m.z = (m.z & 0x80000000u) | 1u;
+                }
+            }
+        }
+        ray_d[gid] = out_d;
+        meta[gid] = m;
+    }
+    const uint32_t sslot = block_compact_slot(shadow, sh_count);
+    if (shadow) {
+        sh_o[sslot] = so;
+        sh_path[sslot] = (uint32_t)gid;
+    }
+    const uint32_t slot = block_compact_slot(survive, next_count);
+    if (survive) next_queue[slot] = (uint32_t)gid;
+    flush_counts(dc, tc, COUNT);
+}
+
 // Stage 4: film accumulation (worker.rs:42): film[pixel] += (L, L, L, alpha), the pass's samples in sample order.
 __global__ void __launch_bounds__(128) wf_accumulate_kernel(TileMap tm, float4* __restrict__ film, const float4* __restrict__ ray_d,
                                                             const uint4* __restrict__ meta, uint32_t n_samples, unsigned long long batch_threads) {
