@@ -231,7 +231,8 @@ int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant);
  * DECODED   = the dequantisation hoisted to upload time: f32 child boxes (256 B per node) and f32 v0 / e1 / e2 per triangle
  *             (288 B per packet), written once by a device kernel with the same fma — ~2x fewer instructions per visit, best
  *             for coherent rays (issue-bound);
- * AUTO      = DECODED for the thread-per-ray kernels on camera rays and the megakernel, QUANTISED for PERSIST / POOL (default). */
+ * AUTO      = DECODED for the thread-per-ray kernels on camera rays and the megakernel, QUANTISED for PERSIST / POOL unless the
+ *             decoded BVH is at most 1 MB (default). */
 #define MP_LAYOUT_QUANTISED 0u
 #define MP_LAYOUT_DECODED 1u
 #define MP_LAYOUT_AUTO 2u

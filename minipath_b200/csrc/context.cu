@@ -40,6 +40,7 @@ struct MpCtx {
     uint32_t trace_variant = MP_TRACE_THREAD;
     uint32_t layout = MP_LAYOUT_AUTO;     // requested node layout
     bool decoded_ok = false;              // the decoded arrays exist and passed the min <= max check
+    bool decoded_small = false;           // decoded BVH <= 1 MB: it stays L1/L2-hot and many lanes share a node, so even the pool kernels prefer it
     uint32_t* d_flags = nullptr;
     int sm_count = 148;
     int octet_bps = 0;
@@ -388,6 +389,7 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaGetLastError());
     ctx->decoded_ok = h_flags == 0;  // a child box with min > max: stay on the quantised records
+    ctx->decoded_small = s_inner_w + s_pack_w <= (1u << 20);
     ctx->max_stack = st.max_stack;
     ctx->has_scene = true;
     return MP_OK;
