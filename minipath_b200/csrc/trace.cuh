@@ -87,7 +87,7 @@ __device__ __forceinline__ bool tri_lane(const uint4 (&q)[9], int lane, const F3
     F3 e1 = v1 - v0, e2 = v2 - v0;
     F3 p = fma_cross(r.d, e2);
     float det = fma_dot(e1, p);
-    float inv = __fdiv_rn(1.0f, det);  // may be infinite; no epsilon test in the reference
+    float inv = __frcp_rn(det);  // = 1.0f / det correctly rounded (triangle.rs:203); may be infinite, no epsilon test in the reference
     F3 s = r.o - v0;
     float u = __fmul_rn(inv, fma_dot(s, p));
     F3 qv = fma_cross(s, e1);
