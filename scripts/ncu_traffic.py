@@ -20,7 +20,7 @@ def main(path, key):
     for r in rows[1:]:
         d = per.setdefault(r[idi], {"name": r[ki]})
         d[r[mi]] = float(r[vi].replace(",", "")) * scale.get(r[ui], 1)
-    trav = re.compile(r"(wf_trace|wf_shadow|render_mega|trace_rays)")
+    trav = re.compile(r"(wf_trace|wf_shadow|wf_primary|render_mega|trace_rays)")
     # the timed step launches the COUNT=false instantiations (last template argument 0 / false); the counted pass the others
     timed = [d for d in per.values() if trav.search(d["name"]) and re.search(r"<[^>]*(, 0|false)>\(", d["name"].replace("(bool)", ""))]
     out = {"dram_bytes_per_step": sum(d.get("dram__bytes_read.sum", 0) + d.get("dram__bytes_write.sum", 0) for d in timed),
