@@ -11,6 +11,7 @@
 #include <fstream>
 #include <map>
 #include <sstream>
+#include <thread>
 #include <tuple>
 #include <vector>
 
@@ -37,6 +38,8 @@ struct VertexData {  // building.rs:220-224
 };
 struct Tri {
     uint32_t v[3];
+    V3 c;           // centroid and bounds, filled once by build_flat: the builders sort triangles many times and would
+    V3 bmin, bmax;  // otherwise gather the three vertices (a cache miss each) at every level
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -132,7 +135,7 @@ static int load_obj(const char* path, int quad_mode, std::vector<Tri>& triangles
                 }
                 poly.push_back(id);
             }
-            for (size_t k = 2; k < poly.size(); ++k) triangles.push_back(Tri{{poly[0], poly[k - 1], poly[k]}});
+            for (size_t k = 2; k < poly.size(); ++k) triangles.push_back(Tri{{poly[0], poly[k - 1], poly[k]}, V3{}, V3{}, V3{}});
         }
     }
     if (skipped) fprintf(stderr, "minipath_b200: %zu non-triangle primitive(s) skipped in %s\n", skipped, path);
