@@ -137,7 +137,12 @@ __device__ __forceinline__ float4 render_sample(const Scene& sc, const Camera& c
 
 // Worker::render_tile for many tiles (worker.rs:32-49): one thread per pixel, samples summed sequentially.
 template <int LAYOUT, int ORDER, bool COUNT>
-__global__ void __launch_bounds__(128) render_mega_kernel(Scene sc, Camera cam, TileMap tm, float4* __restrict__ film, uint32_t width,
+// 6 blocks (24 warps) per SM = 80 registers with ~300 B of spills: +8 % over the unconstrained 128 registers / 16 warps on teapot and cube
+// (profiles/r1f_variants_primary_ab2.json; 5, 7 and 8 blocks measured slower) - the kernel waits on fixed-latency dependencies, not on memory.
+#ifndef MEGA_MIN_BLOCKS
+#define MEGA_MIN_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(128, MEGA_MIN_BLOCKS) render_mega_kernel(Scene sc, Camera cam, TileMap tm, float4* __restrict__ film, uint32_t width,
                                                           uint32_t sample_base, uint32_t sample_count, uint32_t max_bounces,
                                                           uint32_t seed_hash, DevCounters* dc) {
     const unsigned long long gid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
