@@ -440,9 +440,9 @@ def roofline(args, res):
         "kernel": {"megakernel": "render_mega_kernel", "wavefront-octet": "wf_trace_octet_kernel+wf_shadow_octet_kernel",
                    "wavefront-thread": "wf_trace_kernel+wf_shadow_kernel",
                    "wavefront-persist": "wf_trace_persist_kernel+wf_shadow_persist_kernel",
-                   "wavefront-hybrid": "wf_trace_kernel (camera rays) + wf_trace_persist_kernel+wf_shadow_persist_kernel",
+                   "wavefront-hybrid": "wf_primary_kernel (camera rays: ray-gen + trace + shade) + wf_trace_persist_kernel+wf_shadow_persist_kernel",
                    "wavefront-pool": "wf_trace_pool_kernel+wf_shadow_pool_kernel",
-                   "wavefront-hybrid-pool": "wf_trace_kernel (camera rays) + wf_trace_pool_kernel+wf_shadow_pool_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
+                   "wavefront-hybrid-pool": "wf_primary_kernel (camera rays: ray-gen + trace + shade) + wf_trace_pool_kernel+wf_shadow_pool_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
         "peak_source": "FP32 FMA and L2 read bandwidth measured by mp_probe_* in this run; HBM " + hbm_src,
         "fp32": {"achieved_tflops": flops / secs / 1e12, "peak_tflops": fp32, "frac": t_fp32 / secs},
         "l2": {"achieved_gbs": bytes_ / secs / 1e9, "peak_gbs": l2, "frac": t_l2 / secs},
