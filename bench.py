@@ -48,7 +48,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="teapot-1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", default="auto", choices=["auto", "megakernel", "wavefront-octet", "wavefront-thread", "wavefront-persist", "wavefront-hybrid", "wavefront-pool",
-                                                     "wavefront-hybrid-pool"],
+                                                     "wavefront-hybrid-pool", "wavefront-hybrid-pool-s0"],
                     help="megakernel: one thread per pixel; wavefront-*: staged kernels with the thread-per-ray, the 8-lanes-per-ray "
                          "(octet) or the persistent phased thread-per-ray traversal kernel")
     ap.add_argument("--order", default="reference", choices=["reference", "near_first"])
@@ -243,10 +243,12 @@ def run_b200(args, rank, local, world):
 
     modes = {"megakernel": mp.MODE_MEGAKERNEL, "wavefront-thread": mp.MODE_WAVEFRONT, "wavefront-octet": mp.MODE_WAVEFRONT,
              "wavefront-persist": mp.MODE_WAVEFRONT, "wavefront-hybrid": mp.MODE_WAVEFRONT,
-             "wavefront-pool": mp.MODE_WAVEFRONT, "wavefront-hybrid-pool": mp.MODE_WAVEFRONT}
+             "wavefront-pool": mp.MODE_WAVEFRONT, "wavefront-hybrid-pool": mp.MODE_WAVEFRONT,
+             "wavefront-hybrid-pool-s0": mp.MODE_WAVEFRONT}
     variants = {"megakernel": mp.TRACE_THREAD, "wavefront-thread": mp.TRACE_THREAD, "wavefront-octet": mp.TRACE_OCTET,
                 "wavefront-persist": mp.TRACE_PERSIST, "wavefront-hybrid": mp.TRACE_HYBRID,
-                "wavefront-pool": mp.TRACE_POOL, "wavefront-hybrid-pool": mp.TRACE_HYBRID_POOL}
+                "wavefront-pool": mp.TRACE_POOL, "wavefront-hybrid-pool": mp.TRACE_HYBRID_POOL,
+                "wavefront-hybrid-pool-s0": mp.TRACE_HYBRID_POOL_S0}
     if bvh.stats()["max_stack"] > 128:  # deeper than the local-memory stack of the thread-per-ray kernels
         modes = {"wavefront-octet": mp.MODE_WAVEFRONT, "wavefront-pool": mp.MODE_WAVEFRONT}
 
@@ -442,7 +444,8 @@ def roofline(args, res):
                    "wavefront-persist": "wf_trace_persist_kernel+wf_shadow_persist_kernel",
                    "wavefront-hybrid": "wf_primary_kernel (camera rays: ray-gen + trace + shade) + wf_trace_persist_kernel+wf_shadow_persist_kernel",
                    "wavefront-pool": "wf_trace_pool_kernel+wf_shadow_pool_kernel",
-                   "wavefront-hybrid-pool": "wf_primary_kernel (camera rays: ray-gen + trace + shade) + wf_trace_pool_kernel+wf_shadow_pool_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
+                   "wavefront-hybrid-pool": "wf_primary_kernel (camera rays: ray-gen + trace + shade) + wf_trace_pool_kernel+wf_shadow_pool_kernel",
+                   "wavefront-hybrid-pool-s0": "wf_primary_kernel<SHADOW0> (camera rays + depth-0 sun rays: ray-gen + trace + shade + any-hit) + wf_trace_pool_kernel+wf_shadow_pool_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
         "peak_source": "FP32 FMA and L2 read bandwidth measured by mp_probe_* in this run; HBM " + hbm_src,
         "fp32": {"achieved_tflops": flops / secs / 1e12, "peak_tflops": fp32, "frac": t_fp32 / secs},
         "l2": {"achieved_gbs": bytes_ / secs / 1e9, "peak_gbs": l2, "frac": t_l2 / secs},

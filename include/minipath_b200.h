@@ -223,6 +223,10 @@ int mp_ctx_sync(MpCtx* ctx);
  * kind (inner node / triangle packet) in lockstep per round (pool.cuh); HYBRID_POOL = THREAD for camera rays, POOL after */
 #define MP_TRACE_POOL 4u
 #define MP_TRACE_HYBRID_POOL 5u
+/* HYBRID_POOL_S0 = HYBRID_POOL whose camera-ray kernel also traces the depth-0 sun rays in place (they leave neighbouring
+ * pixels' hit points in ONE direction, so they are as coherent as the camera rays): no queue round trip and no pool launch
+ * for the largest shadow batch of a pass.  Same film, same counters. */
+#define MP_TRACE_HYBRID_POOL_S0 6u
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant);
 /* Node layout the THREAD / PERSIST / POOL kernels and the megakernel read (same results, bit for bit):
  * QUANTISED = the reference records (InnerNode 128 B, RelativeTriangle8 144 B; u16 → f32 on every visit,

@@ -22,6 +22,7 @@ from ._ffi import (  # noqa: F401  (re-exported)
     ORDER_REFERENCE,
     TRACE_HYBRID,
     TRACE_HYBRID_POOL,
+    TRACE_HYBRID_POOL_S0,
     TRACE_POOL,
     TRACE_OCTET,
     TRACE_PERSIST,

@@ -253,7 +253,7 @@ int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream) {
 
 int mp_ctx_set_trace_variant(MpCtx* ctx, uint32_t variant) {
     if (!ctx) return fail(MP_EINVAL, "null context");
-    if (variant > MP_TRACE_HYBRID_POOL) return fail(MP_EINVAL, "bad trace variant %u", variant);
+    if (variant > MP_TRACE_HYBRID_POOL_S0) return fail(MP_EINVAL, "bad trace variant %u", variant);
     ctx->trace_variant = variant;
     return MP_OK;
 }

@@ -206,7 +206,7 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
     if (!scene || !camera || !settings || !out) return fail(MP_EINVAL, "null argument");
     if (settings->tile_size == 0 || settings->sample_count == 0) return fail(MP_EINVAL, "tile_size and sample_count must be non-zero (NonZeroU32)");
     if (settings->resolution_x == 0 || settings->resolution_y == 0) return fail(MP_EINVAL, "empty resolution");
-    if (settings->trace_kernel > MP_TRACE_HYBRID_POOL + 1) return fail(MP_EINVAL, "bad trace_kernel");
+    if (settings->trace_kernel > MP_TRACE_HYBRID_POOL_S0 + 1) return fail(MP_EINVAL, "bad trace_kernel");
     int have = 0;
     if (int rc = mp_device_count(&have)) return rc;
     if (have == 0) return fail(MP_ENODEVICE, "no CUDA device available; this library has no CPU fallback");

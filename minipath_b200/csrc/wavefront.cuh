@@ -259,7 +259,10 @@ __global__ void __launch_bounds__(128) wf_shadow_kernel(Scene sc, const float4* 
 // a path writes its direction + radiance and its meta word once, and only the survivors write an origin and queue entries.
 // The memory left behind is exactly what wf_raygen + wf_trace + wf_shade at depth 0 leave (minus the hit record, which only the
 // shade stage of the same depth reads), so the later stages are unchanged.
-template <int LAYOUT, int ORDER, bool COUNT>
+// SHADOW0: the depth-0 sun ray (wf_shadow_kernel of depth 0) is traced here too instead of being queued: the shadow rays of one warp
+// start on neighbouring pixels' hit points and share ONE direction, so the thread-per-ray traversal stays coherent; the contribution
+// is added to L before anything else is (the order wf_shadow_kernel of depth 0 adds it in), so the film does not change.
+template <int LAYOUT, int ORDER, bool COUNT, bool SHADOW0>
 __global__ void __launch_bounds__(128, WF_PRIMARY_MIN_BLOCKS) wf_primary_kernel(Scene sc, Camera cam, TileMap tm, uint32_t width, uint32_t sample_first, uint32_t n_samples,
                                                          unsigned long long batch_threads, uint32_t seed_hash, uint32_t max_bounces,
                                                          float4* __restrict__ ray_o, float4* __restrict__ ray_d, uint4* __restrict__ meta,
@@ -327,17 +330,24 @@ __global__ void __launch_bounds__(128, WF_PRIMARY_MIN_BLOCKS) wf_primary_kernel(
                 }
             }
         }
+        if (SHADOW0 && shadow) {  // ---- wf_shadow_kernel at depth 0 ----
+            const Ray sr = ray_new(f3(so.x, so.y, so.z), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
+            tc.rays += 1, tc.shadow_rays += 1;
+            const Hit sh = trace<LAYOUT, ORDER, COUNT>(sc, sr, true, tc.vis);
+            if (sh.tri == MP_NO_HIT) out_d.w = __fadd_rn(out_d.w, so.w);
+            shadow = false;
+        }
         ray_d[gid] = out_d;
         meta[gid] = m;
     }
 #if WF_PRIMARY_WARP_COMPACT
-    const uint32_t sslot = warp_compact_slot(shadow, sh_count);
+    const uint32_t sslot = SHADOW0 ? 0u : warp_compact_slot(shadow, sh_count);
     const uint32_t slot = warp_compact_slot(survive, next_count);
 #else
-    const uint32_t sslot = block_compact_slot(shadow, sh_count);
+    const uint32_t sslot = SHADOW0 ? 0u : block_compact_slot(shadow, sh_count);
     const uint32_t slot = block_compact_slot(survive, next_count);
 #endif
-    if (shadow) {
+    if (!SHADOW0 && shadow) {
         sh_o[sslot] = so;
         sh_path[sslot] = (uint32_t)gid;
     }

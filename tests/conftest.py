@@ -52,7 +52,7 @@ def cube_camera():
     return mp.Camera.default().look_at((1.5, 1.2, 2.5), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0)).f_number(64.0)
 
 
-@pytest.fixture(scope="session", params=["pool", "hybrid_pool", "hybrid", "persist", "octet", "thread", "pool-d", "persist-d", "thread-q", "hybrid_pool-q"])
+@pytest.fixture(scope="session", params=["pool", "hybrid_pool", "hybrid_pool_s0", "hybrid", "persist", "octet", "thread", "pool-d", "persist-d", "thread-q", "hybrid_pool-q"])
 def gpu_ctx(request):
     """One device context per traversal-kernel variant: every GPU parity test runs against both."""
     import minipath_b200 as mp
@@ -61,7 +61,7 @@ def gpu_ctx(request):
         pytest.fail("no CUDA device: -m gpu tests need a B200 (there is no CPU fallback)")
     ctx = mp.Context(0)
     name, _, forced = request.param.partition("-")
-    ctx.set_trace_variant({"octet": mp.TRACE_OCTET, "thread": mp.TRACE_THREAD, "persist": mp.TRACE_PERSIST, "hybrid": mp.TRACE_HYBRID, "pool": mp.TRACE_POOL, "hybrid_pool": mp.TRACE_HYBRID_POOL}[name])
+    ctx.set_trace_variant({"octet": mp.TRACE_OCTET, "thread": mp.TRACE_THREAD, "persist": mp.TRACE_PERSIST, "hybrid": mp.TRACE_HYBRID, "pool": mp.TRACE_POOL, "hybrid_pool": mp.TRACE_HYBRID_POOL, "hybrid_pool_s0": mp.TRACE_HYBRID_POOL_S0}[name])
     # default node layout is AUTO (decoded f32 boxes / edges for thread-per-ray kernels, quantised records for persist / pool);
     # "-d" / "-q" force one layout for every kernel of the variant
     ctx.set_node_layout({"": mp.LAYOUT_AUTO, "d": mp.LAYOUT_DECODED, "q": mp.LAYOUT_QUANTISED}[forced])
