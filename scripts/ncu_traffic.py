@@ -21,13 +21,17 @@ def main(path, key):
         d = per.setdefault(r[idi], {"name": r[ki]})
         d[r[mi]] = float(r[vi].replace(",", "")) * scale.get(r[ui], 1)
     trav = re.compile(r"(wf_trace|wf_shadow|wf_primary|render_mega|trace_rays)")
-    # the timed step launches the COUNT=false instantiations (last template argument 0 / false); the counted pass the others
-    timed = [d for d in per.values() if trav.search(d["name"]) and re.search(r"<[^>]*(, 0|false)>\(", d["name"].replace("(bool)", ""))]
+    # the timed step launches the COUNT=false instantiations (template argument 3 of <LAYOUT, ORDER, COUNT[, SHADOW0]>, 2 of the octet
+    # kernels' <ORDER, COUNT>); the counted pass the others
+    timed = [d for d in per.values() if trav.search(d["name"]) and re.search(r"<(\d+, \d+, (0|false)(, \w+)?|\d+, (0|false))>\(", d["name"].replace("(bool)", "").replace("(int)", ""))]
     out = {"dram_bytes_per_step": sum(d.get("dram__bytes_read.sum", 0) + d.get("dram__bytes_write.sum", 0) for d in timed),
            "traversal_seconds_under_ncu": sum(d.get("gpu__time_duration.sum", 0) for d in timed), "launches": len(timed),
            "kernels": sorted({d["name"].split("(")[0] for d in timed}), "source": os.path.basename(path)}
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     allv = json.load(open(tp)) if os.path.exists(tp) else {}
+    if len(sys.argv) > 3:  # captured at a reduced spp: bench.py scales linearly
+        out["spp"] = int(sys.argv[3])
+        out["note"] = f"captured at --spp {sys.argv[3]} (one pass); scales linearly with spp"
     allv[key] = out
     json.dump(allv, open(tp, "w"), indent=1, sort_keys=True)
     print(key, out)
