@@ -175,6 +175,10 @@ typedef struct MpHit { /* LeafHitRecord (ray_bvh_intersection.rs:165-171) withou
 
 #define MP_MODE_MEGAKERNEL 0u /* one thread per pixel runs the whole sample loop */
 #define MP_MODE_WAVEFRONT 1u  /* ray-gen → trace → shade → compact → … → film accumulate */
+/* mp_render only: the library picks the pipeline from the scene and the settings — the megakernel for the reference's own
+ * workload (max_bounces = 0) and for scenes that are a single leaf, else the wavefront pipeline with MP_TRACE_HYBRID_POOL_S0
+ * (MP_TRACE_POOL when the BVH is deeper than the thread-per-ray kernels' 128-entry stack).  Same film whatever is picked. */
+#define MP_MODE_AUTO 2u
 #define MP_ORDER_REFERENCE 0u /* exact LIFO / lane order of ray_bvh_intersection.rs:39-64,161 (bit-exact gate) */
 #define MP_ORDER_NEAR_FIRST 1u /* children pushed far→near; not bit-pinned, mismatches are reported */
 
@@ -310,7 +314,7 @@ typedef struct MpRenderSettings { /* renderer/mod.rs:7-13 + extension fields wit
     uint32_t sample_count;
     uint32_t resolution_x, resolution_y;
     uint32_t max_bounces; /* 0 → reference behaviour */
-    uint32_t mode;        /* MP_MODE_* */
+    uint32_t mode;        /* MP_MODE_*, incl. MP_MODE_AUTO */
     uint32_t order;       /* MP_ORDER_* */
     uint32_t tiles_per_batch; /* 0 → default */
     uint32_t trace_kernel;    /* 0 → chosen by the library; otherwise MP_TRACE_* + 1 */

@@ -15,6 +15,7 @@ from ._ffi import (  # noqa: F401  (re-exported)
     LAYOUT_AUTO,
     LAYOUT_DECODED,
     LAYOUT_QUANTISED,
+    MODE_AUTO,
     MODE_MEGAKERNEL,
     MODE_WAVEFRONT,
     NO_HIT,
@@ -203,22 +204,23 @@ class Camera:
 class RenderSettings:
     """renderer/mod.rs:7-13 plus extension fields whose defaults reproduce the reference (0 bounces, OS seed)."""
 
-    def __init__(self, tile_size, sample_count, resolution, max_bounces=0, seed=0, mode=MODE_MEGAKERNEL, order=ORDER_REFERENCE,
+    def __init__(self, tile_size, sample_count, resolution, max_bounces=0, seed=0, mode=None, order=ORDER_REFERENCE,
                  tiles_per_batch=0, trace_kernel=None):
         if tile_size <= 0 or sample_count <= 0:
             raise ValueError("tile_size and sample_count are NonZeroU32")
         self.tile_size, self.sample_count = int(tile_size), int(sample_count)
         self.resolution = (int(resolution[0]), int(resolution[1]))
-        self.max_bounces, self.seed, self.mode, self.order = int(max_bounces), int(seed), int(mode), int(order)
+        self.max_bounces, self.seed, self.order = int(max_bounces), int(seed), int(order)
+        self.mode = None if mode is None else int(mode)  # None: render() lets the library pick (MODE_AUTO); the per-context calls use the megakernel
         self.tiles_per_batch = int(tiles_per_batch)
         self.trace_kernel = trace_kernel  # None: chosen by the library; else TRACE_THREAD / TRACE_OCTET / TRACE_PERSIST
 
     def _raw(self):
-        return _ffi.MpRenderSettings(self.tile_size, self.sample_count, self.resolution[0], self.resolution[1], self.max_bounces, self.mode,
+        return _ffi.MpRenderSettings(self.tile_size, self.sample_count, self.resolution[0], self.resolution[1], self.max_bounces, MODE_AUTO if self.mode is None else self.mode,
                                      self.order, self.tiles_per_batch, 0 if self.trace_kernel is None else self.trace_kernel + 1, 0, self.seed)
 
     def params(self, sample_count=None, sample_base=0):
-        return _ffi.MpRenderParams(self.sample_count if sample_count is None else sample_count, sample_base, self.max_bounces, self.mode,
+        return _ffi.MpRenderParams(self.sample_count if sample_count is None else sample_count, sample_base, self.max_bounces, MODE_MEGAKERNEL if self.mode is None else self.mode,
                                    self.order, self.tile_size, self.seed)
 
 

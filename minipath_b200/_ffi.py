@@ -18,6 +18,7 @@ NO_HIT = 0xFFFFFFFF
 TRI_FLAT = 0x80000000
 MODE_MEGAKERNEL, MODE_WAVEFRONT = 0, 1
 ORDER_REFERENCE, ORDER_NEAR_FIRST = 0, 1
+MODE_AUTO = 2
 TRACE_THREAD, TRACE_OCTET, TRACE_PERSIST, TRACE_HYBRID, TRACE_POOL, TRACE_HYBRID_POOL, TRACE_HYBRID_POOL_S0 = 0, 1, 2, 3, 4, 5, 6
 LAYOUT_QUANTISED, LAYOUT_DECODED, LAYOUT_AUTO = 0, 1, 2
 

@@ -28,6 +28,7 @@ pub const MP_TRI_FLAT: u32 = 0x8000_0000;
 
 pub const MP_MODE_MEGAKERNEL: u32 = 0;
 pub const MP_MODE_WAVEFRONT: u32 = 1;
+pub const MP_MODE_AUTO: u32 = 2;
 pub const MP_ORDER_REFERENCE: u32 = 0;
 pub const MP_ORDER_NEAR_FIRST: u32 = 1;
 pub const MP_TRACE_THREAD: u32 = 0;

@@ -57,7 +57,8 @@ where
         resolution_y: settings.resolution.y,
         max_bounces: settings.max_bounces,
         seed: settings.seed.unwrap_or(0),
-        ..Default::default() // mode, order, batch size and traversal kernel: chosen by the library
+        mode: sys::MP_MODE_AUTO, // pipeline and traversal kernel: chosen by the library from the scene and max_bounces
+        ..Default::default()
     };
     let mut handle = std::ptr::null_mut();
     ok(unsafe { sys::mp_render(&flat.raw, &cam, &st, std::ptr::null(), 0, Some(on_started::<F1, F2>), Some(on_finished::<F1, F2>), user, &mut handle) })?;

@@ -53,3 +53,16 @@ def test_product_does_not_touch_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".inc")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "liboracle" not in text and "oracle_lib" not in text and "orc_" not in text, f
+
+
+def test_render_rejects_bad_mode_and_kernel():
+    """Invalid settings are MP_EINVAL (where the reference would panic), checked before any device is touched."""
+    import minipath_b200 as mp
+
+    bvh = mp.TriangleBvh.with_obj(os.path.join(ROOT, "data", "teapot.obj"))
+    for kw in ({"mode": 3}, {"trace_kernel": mp.TRACE_HYBRID_POOL_S0 + 1}, {"order": 2}):
+        with pytest.raises(mp.MpError) as e:
+            mp.render(mp.Scene(bvh), mp.Camera.default(), mp.RenderSettings(64, 1, (64, 64), **kw))
+        assert e.value.code == mp._ffi.MP_EINVAL, kw
+    assert mp.RenderSettings(64, 1, (64, 64))._raw().mode == mp.MODE_AUTO
+    assert mp.RenderSettings(64, 1, (64, 64)).params().mode == mp.MODE_MEGAKERNEL

@@ -174,6 +174,26 @@ def test_render_api_matches_oracle(oracle, teapot, teapot_camera):
     assert np.array_equal(img, oracle.resolve_rgba8(film_cpu, 4))
 
 
+@pytest.mark.parametrize("bounces", [0, 3])
+def test_render_api_auto_pipeline_matches_oracle(oracle, teapot, teapot_camera, bounces):
+    """render() with default settings lets the library pick the pipeline (MP_MODE_AUTO: the megakernel for the reference's own
+    primary-ray workload, the wavefront pipeline with pooled bounce rays and in-place depth-0 sun rays otherwise); the image is the
+    oracle's either way, and the same as with an explicitly chosen pipeline."""
+    w, h = 200, 136  # ragged against the 64-pixel tiles
+    st = mp.RenderSettings(64, 5, (w, h), max_bounces=bounces, seed=4242)
+    assert st.mode is None and st._raw().mode == mp.MODE_AUTO
+    prog = mp.render(mp.Scene(teapot), teapot_camera, st, devices=[0])
+    prog.wait()
+    img = prog.image().copy()
+    tiles = mp.full_screen_tiles(w, h, 64)
+    film_cpu, _, _ = oracle.render_tiles(teapot, teapot_camera.build_sampler((w, h)), w, h, tiles, st.params())
+    assert np.array_equal(img, oracle.resolve_rgba8(film_cpu, 5))
+    st2 = mp.RenderSettings(64, 5, (w, h), max_bounces=bounces, seed=4242, mode=mp.MODE_WAVEFRONT, trace_kernel=mp.TRACE_THREAD)
+    prog2 = mp.render(mp.Scene(teapot), teapot_camera, st2, devices=[0])
+    prog2.wait()
+    assert np.array_equal(img, prog2.image())
+
+
 def test_full_size_properties(gpu_ctx, teapot, teapot_camera):
     """BASELINE.json configs[0] at full size (2048x1536, 10 spp) through size-independent properties: alpha is the
     hit fraction in [0,1], colour <= alpha, the image is left-right plausible, and two runs are identical."""
