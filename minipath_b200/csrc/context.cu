@@ -45,7 +45,7 @@ struct MpCtx {
     int sm_count = 148;
     int octet_bps = 0;
     int persist_bps = 0;
-    int pool_bps = 0;
+    int pool_bps[2] = {0, 0};  // resident pool blocks per SM, [QUANTISED, DECODED] instantiation
     uint2* pool_scratch = nullptr;
     size_t pool_scratch_cap = 0;
     uint32_t* d_claim = nullptr;

@@ -27,6 +27,11 @@ namespace mpd {
 #ifndef POOL_MIN_BLOCKS
 #define POOL_MIN_BLOCKS 5  // resident blocks per SM the register allocation aims at; measured: 6 (80 regs) and 8 (64 regs, 64-ray pools) are 3-15 % slower
 #endif
+#ifndef POOL_MIN_BLOCKS_DECODED
+#define POOL_MIN_BLOCKS_DECODED 4  // the DECODED instantiations serve BVHs of at most 1 MB (AUTO layout), which live in L1: there 4 blocks (102 registers)
+                                   // beat 5 (96): default workload 32.0 -> 30.0 ms, while the stand-in (QUANTISED records) loses 10 % with 4
+#endif
+#define POOL_BLOCKS_FOR(LAYOUT) ((LAYOUT) == MP_LAYOUT_DECODED ? POOL_MIN_BLOCKS_DECODED : POOL_MIN_BLOCKS)
 #ifndef POOL_SS
 #define POOL_SS 0       // entries of every ray's stack kept in shared memory (power of two, 0 = none); the rest lives in the global scratch.
                         // Measured on the stand-in (8 spp, ms per frame): 0 -> 79.4, 2 -> 85.8, 4 -> 86.7: the ring bookkeeping in the unrolled
@@ -301,7 +306,7 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
 // ---- kernels: 128 threads = 4 pools per block, persistent grid ----
 
 template <int LAYOUT, int ORDER, bool COUNT>
-__global__ void __launch_bounds__(128, POOL_MIN_BLOCKS) trace_rays_pool_kernel(Scene sc, const float* __restrict__ rays, uint32_t n, uint4* __restrict__ hits,
+__global__ void __launch_bounds__(128, POOL_BLOCKS_FOR(LAYOUT)) trace_rays_pool_kernel(Scene sc, const float* __restrict__ rays, uint32_t n, uint4* __restrict__ hits,
                                                               DevCounters* dc, uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];
     ThreadCounts tc{};
@@ -318,7 +323,7 @@ __global__ void __launch_bounds__(128, POOL_MIN_BLOCKS) trace_rays_pool_kernel(S
 }
 
 template <int LAYOUT, int ORDER, bool COUNT>
-__global__ void __launch_bounds__(128, POOL_MIN_BLOCKS) wf_trace_pool_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
+__global__ void __launch_bounds__(128, POOL_BLOCKS_FOR(LAYOUT)) wf_trace_pool_kernel(Scene sc, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count,
                                                             const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
                                                             uint4* __restrict__ hit, DevCounters* dc, uint32_t* claim, uint2* scratch,
                                                             uint32_t stack_cap) {
@@ -335,7 +340,7 @@ __global__ void __launch_bounds__(128, POOL_MIN_BLOCKS) wf_trace_pool_kernel(Sce
 }
 
 template <int LAYOUT, int ORDER, bool COUNT>
-__global__ void __launch_bounds__(128, POOL_MIN_BLOCKS) wf_shadow_pool_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
+__global__ void __launch_bounds__(128, POOL_BLOCKS_FOR(LAYOUT)) wf_shadow_pool_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
                                                              const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, DevCounters* dc,
                                                              uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];
