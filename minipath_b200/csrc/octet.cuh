@@ -225,6 +225,10 @@ __device__ __forceinline__ void octet_run(const Scene& sc, const SceneCM& cm, ui
             if (lf_rem != 0) {
                 if (eq && tw < lf_local.t) lf_local = Hit{tw, uw, vw, lf_index * 8u + win};
                 ++lf_index;
+                if (any_hit && lf_rem > 1 && lf_local.t < lf_max_t) {  // occluded: skip the leaf's remaining packets
+                    if (COUNT) tc.vis.packets -= lf_rem - 1u;
+                    lf_rem = 1;
+                }
                 if (--lf_rem == 0 && lf_local.t < best.t) {  // :59
                     best = lf_local;
                     if (any_hit) sp = 0;

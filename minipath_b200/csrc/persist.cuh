@@ -77,6 +77,10 @@ __device__ __forceinline__ void persist_run(const Scene& sc, uint32_t n, uint32_
             // ---- one packet of the leaf (ray_bvh_intersection.rs:104-141) ----
             visit_packet<LAYOUT>(sc, r, p_index, lf_max_t, lf_local);
             ++p_index;
+            if (any_hit && lf_rem > 1 && lf_local.t < lf_max_t) {  // occluded: skip the leaf's remaining packets
+                if (COUNT) tc.vis.packets -= lf_rem - 1u;
+                lf_rem = 1;
+            }
             if (--lf_rem == 0) {
                 kind = 0;
                 if (lf_local.t < best.t) {  // :59

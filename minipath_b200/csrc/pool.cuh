@@ -281,6 +281,10 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
                 Hit local{pw.f(PC_LT, slot), pw.f(PC_LU, slot), pw.f(PC_LV, slot), pw.u(PC_LTRI, slot)};
                 visit_packet<LAYOUT>(sc, r, pidx, bt, local);
                 ++pidx, --rem;
+                if (any_hit && rem != 0 && local.t < bt) {  // occluded: skip the leaf's remaining packets
+                    if (COUNT) tc.vis.packets -= rem;
+                    rem = 0;
+                }
                 pw.u(PC_PIDX, slot) = pidx, pw.u(PC_REM, slot) = rem;
                 if (rem == 0) {
                     done = true;

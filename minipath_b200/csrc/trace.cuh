@@ -325,7 +325,13 @@ __device__ __forceinline__ Hit trace_impl(const Scene& sc, const Ray& r, bool an
             if (COUNT) vis.leaves++, vis.packets += count;
             const float max_t = best.t;  // not updated inside the leaf
             Hit local{MPD_INF, 0.0f, 0.0f, MP_NO_HIT};
-            for (uint32_t j = 0; j < count; ++j) visit_packet<LAYOUT>(sc, r, index + j, max_t, local);
+            for (uint32_t j = 0; j < count; ++j) {
+                visit_packet<LAYOUT>(sc, r, index + j, max_t, local);
+                if (any_hit && local.t < max_t) {  // shadow rays (extension): occluded, the remaining packets cannot change that
+                    if (COUNT) vis.packets -= count - 1u - j;
+                    break;
+                }
+            }
             if (local.t < best.t) {  // :59
                 best = local;
                 if (any_hit) break;
