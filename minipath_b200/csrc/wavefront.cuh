@@ -95,6 +95,9 @@ __device__ __forceinline__ uint32_t warp_compact_slot(bool pred, uint32_t* count
 #ifndef WF_PRIMARY_MIN_BLOCKS
 #define WF_PRIMARY_MIN_BLOCKS 6
 #endif
+#ifndef WF_PRIMARY_S0_BLOCK
+#define WF_PRIMARY_S0_BLOCK 0  // 1: SHADOW0 compacts the block's sun rays into its first lanes (two block barriers) instead of tracing them in the owning lanes
+#endif
 
 // Stage 1: CameraSampler::sample_ray (camera.rs:176-191) for `n_samples` consecutive samples of every pixel of the tile batch.
 // Path slot = s * batch_threads + (thread index inside the batch): neighbouring slots are neighbouring pixels of one sample.
@@ -275,6 +278,8 @@ __global__ void __launch_bounds__(128, WF_PRIMARY_MIN_BLOCKS) wf_primary_kernel(
     ThreadCounts tc{};
     bool survive = false, shadow = false;
     float4 so = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint4 m = make_uint4(0u, 0u, 0u, 0u);
+    float4 out_d = make_float4(0.f, 0.f, 0.f, 0.f);
     if (active) {
         const uint32_t pixel_index = y * width + x;
         uint32_t rng = rng_init(pixel_index, sample_first + s, seed_hash);
@@ -283,8 +288,8 @@ __global__ void __launch_bounds__(128, WF_PRIMARY_MIN_BLOCKS) wf_primary_kernel(
         const Hit h = trace<LAYOUT, ORDER, COUNT>(sc, r, false, tc.vis);
         // ---- wf_shade_kernel at depth 0 (T = 1, L = 0) ----
         float T = 1.0f, L = 0.0f;
-        uint4 m = make_uint4(pixel_index, rng, 0u, 0u);
-        float4 out_d = make_float4(r.d.x, r.d.y, r.d.z, 0.0f);
+        m = make_uint4(pixel_index, rng, 0u, 0u);
+        out_d = make_float4(r.d.x, r.d.y, r.d.z, 0.0f);
         if (max_bounces == 0) {  // the reference shader (worker.rs:57-64)
             if (h.tri != MP_NO_HIT) {
                 L = fabsf(dotn(r.d, shading_normal(sc, h)));
@@ -330,6 +335,7 @@ __global__ void __launch_bounds__(128, WF_PRIMARY_MIN_BLOCKS) wf_primary_kernel(
                 }
             }
         }
+#if !WF_PRIMARY_S0_BLOCK
         if (SHADOW0 && shadow) {  // ---- wf_shadow_kernel at depth 0 ----
             const Ray sr = ray_new(f3(so.x, so.y, so.z), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
             tc.rays += 1, tc.shadow_rays += 1;
@@ -337,6 +343,31 @@ __global__ void __launch_bounds__(128, WF_PRIMARY_MIN_BLOCKS) wf_primary_kernel(
             if (sh.tri == MP_NO_HIT) out_d.w = __fadd_rn(out_d.w, so.w);
             shadow = false;
         }
+#endif
+    }
+#if WF_PRIMARY_S0_BLOCK
+    if (SHADOW0) {  // the block's sun rays compacted into its first lanes: full warps trace them instead of the sparse lanes that own them
+        __shared__ float4 s_so[128];
+        __shared__ unsigned char s_lit[128];
+        __shared__ uint32_t s_n;
+        if (threadIdx.x == 0) s_n = 0u;
+        __syncthreads();
+        const uint32_t mine = warp_compact_slot(shadow, &s_n);
+        if (shadow) s_so[mine] = so;
+        __syncthreads();
+        if (threadIdx.x < s_n) {
+            const float4 o = s_so[threadIdx.x];
+            const Ray sr = ray_new(f3(o.x, o.y, o.z), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
+            tc.rays += 1, tc.shadow_rays += 1;
+            const Hit sh = trace<LAYOUT, ORDER, COUNT>(sc, sr, true, tc.vis);
+            s_lit[threadIdx.x] = sh.tri == MP_NO_HIT ? 1 : 0;
+        }
+        __syncthreads();
+        if (shadow && s_lit[mine]) out_d.w = __fadd_rn(out_d.w, so.w);
+        shadow = false;
+    }
+#endif
+    if (active) {
         ray_d[gid] = out_d;
         meta[gid] = m;
     }
