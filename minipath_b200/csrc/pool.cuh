@@ -119,50 +119,55 @@ __device__ __forceinline__ void pool_push(const PoolWarp& pw, PoolQueues& qs, in
 // the entry the inner phase kept in registers instead of pushing it (PoolDeferSink), or the root of a fresh ray — it is the top of
 // the stack and needs no `t1 > best.t` test (t1 <= t2 <= max_t = best.t; the root carries -inf).
 template <bool COUNT, class S, class Emit>
+__device__ __forceinline__ uint32_t pool_next(const PoolWarp& pw, uint32_t slot, S& stk, float best_t, Emit emit, ThreadCounts& tc, bool has_top, uint2 top) {
+    uint32_t kind = 0;  // 0 finished, 1 inner, 2 leaf
+    while (has_top || stk.sp > 0) {
+        uint2 e;
+        if (has_top) {
+            e = top, has_top = false;
+        } else if (S::kShort) {
+            e = stk.pop();
+            if (__uint_as_float(e.y) > best_t) continue;  // ray_bvh_intersection.rs:40
+        } else {
+            // Two entries per iteration, both loads in flight before either is tested: a run of culled entries is otherwise a
+            // chain of dependent L2 round trips (13 % of the kernel's stall samples sat on this test, profiles/r1d_wf_pool_32Mpaths.txt).
+            const int i = stk.sp - 1;
+            const uint2 a = stk.at(i);
+            const uint2 b = stk.at(i > 0 ? i - 1 : 0);
+            stk.sp = i;
+            if (!(__uint_as_float(a.y) > best_t)) {  // ray_bvh_intersection.rs:40
+                e = a;
+            } else if (i > 0 && !(__uint_as_float(b.y) > best_t)) {
+                e = b, stk.sp = i - 1;
+            } else {
+                stk.sp = i > 0 ? i - 1 : 0;
+                continue;
+            }
+        }
+        const uint32_t count = e.x & MP_LINK_COUNT_MASK;
+        pw.u(PC_PIDX, slot) = e.x >> MP_LINK_COUNT_BITS;
+        pw.u(PC_REM, slot) = count;
+        if (count == 0) {
+            kind = 1;
+        } else {
+            kind = 2;
+            pw.f(PC_LT, slot) = MPD_INF;  // max_t of the leaf is best.t, which does not change until the leaf is finished
+            pw.u(PC_LTRI, slot) = MP_NO_HIT;
+            if (COUNT) tc.vis.leaves++, tc.vis.packets += count;
+        }
+        break;
+    }
+    pw.u(PC_SP, slot) = stk.pack();
+    if (kind == 0)
+        emit(pw.u(PC_RID, slot), Hit{pw.f(PC_BT, slot), pw.f(PC_BU, slot), pw.f(PC_BV, slot), pw.u(PC_BTRI, slot)});
+    return kind;
+}
+
+template <bool COUNT, class S, class Emit>
 __device__ __forceinline__ void pool_advance(const PoolWarp& pw, PoolQueues& qs, bool active, uint32_t slot, S& stk, float best_t, Emit emit,
                                              ThreadCounts& tc, bool has_top = false, uint2 top = make_uint2(0u, 0u)) {
     uint32_t kind = 0;  // 0 finished, 1 inner, 2 leaf
-    if (active) {
-        while (has_top || stk.sp > 0) {
-            uint2 e;
-            if (has_top) {
-                e = top, has_top = false;
-            } else if (S::kShort) {
-                e = stk.pop();
-                if (__uint_as_float(e.y) > best_t) continue;  // ray_bvh_intersection.rs:40
-            } else {
-                // Two entries per iteration, both loads in flight before either is tested: a run of culled entries is otherwise a
-                // chain of dependent L2 round trips (13 % of the kernel's stall samples sat on this test, profiles/r1d_wf_pool_32Mpaths.txt).
-                const int i = stk.sp - 1;
-                const uint2 a = stk.at(i);
-                const uint2 b = stk.at(i > 0 ? i - 1 : 0);
-                stk.sp = i;
-                if (!(__uint_as_float(a.y) > best_t)) {  // ray_bvh_intersection.rs:40
-                    e = a;
-                } else if (i > 0 && !(__uint_as_float(b.y) > best_t)) {
-                    e = b, stk.sp = i - 1;
-                } else {
-                    stk.sp = i > 0 ? i - 1 : 0;
-                    continue;
-                }
-            }
-            const uint32_t count = e.x & MP_LINK_COUNT_MASK;
-            pw.u(PC_PIDX, slot) = e.x >> MP_LINK_COUNT_BITS;
-            pw.u(PC_REM, slot) = count;
-            if (count == 0) {
-                kind = 1;
-            } else {
-                kind = 2;
-                pw.f(PC_LT, slot) = MPD_INF;  // max_t of the leaf is best.t, which does not change until the leaf is finished
-                pw.u(PC_LTRI, slot) = MP_NO_HIT;
-                if (COUNT) tc.vis.leaves++, tc.vis.packets += count;
-            }
-            break;
-        }
-        pw.u(PC_SP, slot) = stk.pack();
-        if (kind == 0)
-            emit(pw.u(PC_RID, slot), Hit{pw.f(PC_BT, slot), pw.f(PC_BU, slot), pw.f(PC_BV, slot), pw.u(PC_BTRI, slot)});
-    }
+    if (active) kind = pool_next<COUNT>(pw, slot, stk, best_t, emit, tc, has_top, top);
     pool_push(pw, qs, 0, active && kind == 1, slot);
     pool_push(pw, qs, 1, active && kind == 2, slot);
     pool_push(pw, qs, 2, active && kind == 0, slot);
@@ -307,6 +312,157 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
     }
 }
 
+#ifndef POOL_OWNED_REFILL
+#define POOL_OWNED_REFILL 32u  // free slots in the warp that trigger a refill (one atomicAdd on the launch's claim counter)
+#endif
+// LANE-OWNED POOL (POOL_LANE_OWNED = 1).  In pool_run a round takes ANY 32 of the warp's 96 slots, so the lanes' state accesses
+// (col[c * 96 + slot], bank = slot mod 32) collide: the ncu capture of the stand-in's closest-hit launch counts one bank-conflict replay per
+// shared access (profiles/r1g_pool_atrium_kernel.txt: 305 M loads + 285 M stores, 590 M conflicts), on the same L1 data pipe the node
+// gathers use.  Here lane L owns the slots L, L + 32, L + 64: every state access of a round hits bank L — conflict-free — and the three ring
+// queues with their ballots disappear; a round's kind is voted (lanes that hold an inner item vs lanes that hold a packet item) and every lane
+// runs one of ITS rays that has an item of that kind.  Per ray nothing changes (same visiting order, snapshots and arithmetic).
+template <int LAYOUT, int ORDER, bool COUNT, class Fetch, class Emit>
+__device__ __forceinline__ void pool_run_owned(const Scene& sc, uint32_t n, uint32_t* claim, bool any_hit, uint2* __restrict__ scratch, uint32_t stack_cap,
+                                               unsigned char* smem, Fetch fetch, Emit emit, ThreadCounts& tc) {
+    constexpr uint32_t FULL = 0xffffffffu;
+    constexpr int K = POOL_W / 32;  // slots per lane
+    static_assert(POOL_W % 32 == 0 && K <= 8, "lane-owned pools hold a whole number of slots per lane");
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    PoolWarp pw;
+    pw.col = reinterpret_cast<float*>(smem + (size_t)warp * POOL_SMEM_PER_WARP);
+    pw.ring = nullptr;
+    uint2* const wstacks = scratch + ((size_t)blockIdx.x * POOL_WARPS + warp) * POOL_W * stack_cap;
+    using Stack = PStack<false>;
+    uint32_t kinds = 0;  // 2 bits per owned slot: 0 free, 1 inner item pending, 2 packet item pending
+    bool more = true;    // the input queue may still hold rays
+
+    for (;;) {
+        uint32_t n_free_me = 0;
+        bool has_in = false, has_pk = false;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const uint32_t kd = (kinds >> (2 * k)) & 3u;
+            n_free_me += kd == 0u, has_in |= kd == 1u, has_pk |= kd == 2u;
+        }
+        const uint32_t n_in = __popc(__ballot_sync(FULL, has_in)), n_pk = __popc(__ballot_sync(FULL, has_pk));
+        // ---- refill: at least 32 free slots in the warp, or the next round would run thin ----
+        if (more) {
+            uint32_t incl = n_free_me;  // inclusive scan of the lanes' free-slot counts
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t v = __shfl_up_sync(FULL, incl, d);
+                if (lane >= (uint32_t)d) incl += v;
+            }
+            const uint32_t total = __shfl_sync(FULL, incl, 31);
+            if (total >= POOL_OWNED_REFILL || (total > 0u && n_in < 16u && n_pk < 16u)) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(claim, total);
+                base = __shfl_sync(FULL, base, 0);
+                if (base + total >= n) more = false;  // this claim reaches the end of the queue
+                uint32_t idx = base + (incl - n_free_me);
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    if (((kinds >> (2 * k)) & 3u) != 0u || idx >= n) continue;
+                    const uint32_t slot = (uint32_t)k * 32u + lane;
+                    Ray r;
+                    fetch(idx, r);
+                    pw.f(PC_OX, slot) = r.o.x, pw.f(PC_OY, slot) = r.o.y, pw.f(PC_OZ, slot) = r.o.z;
+                    pw.f(PC_DX, slot) = r.d.x, pw.f(PC_DY, slot) = r.d.y, pw.f(PC_DZ, slot) = r.d.z;
+                    pw.f(PC_IX, slot) = r.inv.x, pw.f(PC_IY, slot) = r.inv.y, pw.f(PC_IZ, slot) = r.inv.z;
+                    pw.f(PC_BT, slot) = MPD_FLT_MAX, pw.f(PC_BU, slot) = 0.0f, pw.f(PC_BV, slot) = 0.0f, pw.u(PC_BTRI, slot) = MP_NO_HIT;
+                    pw.u(PC_RID, slot) = idx;
+                    tc.rays++;
+                    ++idx;
+                    Stack stk{nullptr, wstacks + slot, 0, 0};
+                    const uint32_t kd = pool_next<COUNT>(pw, slot, stk, MPD_FLT_MAX, emit, tc, true, make_uint2(sc.root, __float_as_uint(MPD_NINF)));
+                    kinds |= kd << (2 * k);
+                }
+                continue;
+            }
+        }
+        if (n_in == 0u && n_pk == 0u) break;  // nothing pending; `more` is false here (96 free slots would have been refilled)
+
+        if (n_in >= n_pk) {
+            // ---- one inner node per lane that holds one (ray_bvh_intersection.rs:149-162) ----
+            if (has_in) {
+                int k = 0;
+#pragma unroll
+                for (int j = K - 1; j >= 0; --j)
+                    if (((kinds >> (2 * j)) & 3u) == 1u) k = j;
+                const uint32_t slot = (uint32_t)k * 32u + lane;
+                Stack stk{nullptr, wstacks + slot, 0, 0};
+                stk.unpack(pw.u(PC_SP, slot));
+                const Ray r = pool_load_ray(pw, slot);
+                const float bt = pw.f(PC_BT, slot);
+                const uint32_t node = pw.u(PC_PIDX, slot);
+                if (COUNT) tc.vis.inner++;
+                const bool nanpath = ray_needs_nanpath(r);
+                RaySel sel{};
+                if (LAYOUT == MP_LAYOUT_DECODED && !nanpath) sel = ray_sel(r);
+                bool has_top = false;
+                uint2 top = make_uint2(0u, 0u);
+                if (ORDER == MP_ORDER_REFERENCE) {
+                    PoolDeferSink<Stack> sink{stk, make_uint2(0u, 0u), false};
+                    if (nanpath)
+                        visit_inner<LAYOUT, true>(sc, r, sel, node, bt, sink);
+                    else
+                        visit_inner<LAYOUT, false>(sc, r, sel, node, bt, sink);
+                    has_top = sink.has, top = sink.top;
+                } else {
+                    StackSink<ORDER, Stack> sink{stk, stk.sp, stk.sp};
+                    if (nanpath)
+                        visit_inner<LAYOUT, true>(sc, r, sel, node, bt, sink);
+                    else
+                        visit_inner<LAYOUT, false>(sc, r, sel, node, bt, sink);
+                    stk.sp = sink.sp;
+                }
+                const uint32_t kd = pool_next<COUNT>(pw, slot, stk, bt, emit, tc, has_top, top);
+                kinds = (kinds & ~(3u << (2 * k))) | (kd << (2 * k));
+            }
+        } else if (has_pk) {
+            // ---- one triangle packet per lane that holds one (ray_bvh_intersection.rs:104-141) ----
+            int k = 0;
+#pragma unroll
+            for (int j = K - 1; j >= 0; --j)
+                if (((kinds >> (2 * j)) & 3u) == 2u) k = j;
+            const uint32_t slot = (uint32_t)k * 32u + lane;
+            const Ray r = pool_load_ray(pw, slot);
+            uint32_t pidx = pw.u(PC_PIDX, slot), rem = pw.u(PC_REM, slot);
+            float bt = pw.f(PC_BT, slot);  // = the leaf's max_t: best.t is not updated inside the leaf (:106-107)
+            Hit local{pw.f(PC_LT, slot), pw.f(PC_LU, slot), pw.f(PC_LV, slot), pw.u(PC_LTRI, slot)};
+            visit_packet<LAYOUT>(sc, r, pidx, bt, local);
+            ++pidx, --rem;
+            if (any_hit && rem != 0 && local.t < bt) {  // occluded: skip the leaf's remaining packets
+                if (COUNT) tc.vis.packets -= rem;
+                rem = 0;
+            }
+            pw.u(PC_PIDX, slot) = pidx, pw.u(PC_REM, slot) = rem;
+            if (rem == 0) {
+                Stack stk{nullptr, wstacks + slot, 0, 0};
+                stk.unpack(pw.u(PC_SP, slot));
+                if (local.t < bt) {  // :59
+                    bt = local.t;
+                    pw.f(PC_BT, slot) = local.t, pw.f(PC_BU, slot) = local.u, pw.f(PC_BV, slot) = local.v, pw.u(PC_BTRI, slot) = local.tri;
+                    if (any_hit) stk.clear();
+                }
+                const uint32_t kd = pool_next<COUNT>(pw, slot, stk, bt, emit, tc, false, make_uint2(0u, 0u));
+                kinds = (kinds & ~(3u << (2 * k))) | (kd << (2 * k));
+            } else {
+                pw.f(PC_LT, slot) = local.t, pw.f(PC_LU, slot) = local.u, pw.f(PC_LV, slot) = local.v, pw.u(PC_LTRI, slot) = local.tri;
+            }
+        }
+    }
+}
+
+#ifndef POOL_LANE_OWNED
+#define POOL_LANE_OWNED 0
+#endif
+#if POOL_LANE_OWNED
+#define POOL_RUN pool_run_owned
+#else
+#define POOL_RUN pool_run
+#endif
+
 // ---- kernels: 128 threads = 4 pools per block, persistent grid ----
 
 template <int LAYOUT, int ORDER, bool COUNT>
@@ -314,7 +470,7 @@ __global__ void __launch_bounds__(128, POOL_BLOCKS_FOR(LAYOUT)) trace_rays_pool_
                                                               DevCounters* dc, uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];
     ThreadCounts tc{};
-    pool_run<LAYOUT, ORDER, COUNT>(
+    POOL_RUN<LAYOUT, ORDER, COUNT>(
         sc, n, claim, false, scratch, stack_cap, pool_smem,
         [&](uint32_t i, Ray& r) {
             const float* p = rays + 9 * (size_t)i;
@@ -333,7 +489,7 @@ __global__ void __launch_bounds__(128, POOL_BLOCKS_FOR(LAYOUT)) wf_trace_pool_ke
                                                             uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];
     ThreadCounts tc{};
-    pool_run<LAYOUT, ORDER, COUNT>(
+    POOL_RUN<LAYOUT, ORDER, COUNT>(
         sc, *count, claim, false, scratch, stack_cap, pool_smem,
         [&](uint32_t i, Ray& r) {
             const uint32_t path = queue[i];
@@ -350,7 +506,7 @@ __global__ void __launch_bounds__(128, POOL_BLOCKS_FOR(LAYOUT)) wf_shadow_pool_k
     extern __shared__ __align__(16) unsigned char pool_smem[];
     ThreadCounts tc{};
     const Ray sun = ray_new(f3(0.f, 0.f, 0.f), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
-    pool_run<LAYOUT, ORDER, COUNT>(
+    POOL_RUN<LAYOUT, ORDER, COUNT>(
         sc, *sh_count, claim, true, scratch, stack_cap, pool_smem,
         [&](uint32_t i, Ray& r) {
             const float4 o = sh_o[i];
