@@ -1,5 +1,5 @@
 // CPU restatement of minipath's trace path — TEST INFRASTRUCTURE (see oracle.h for scope and pinning status).
-// Build: g++ -O2 -mavx2 -mfma -ffp-contract=off -shared -fPIC (oracle/Makefile).
+// Build: g++ -O2 -mavx2 -mfma -ffp-contract=off -shared -fPIC (top-level Makefile, target oracle/liboracle.so; __graft_entry__.build()).
 #include "oracle.h"
 
 #include <immintrin.h>
