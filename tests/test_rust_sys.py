@@ -116,3 +116,32 @@ def test_build_rs_uses_the_makefile_flags():
         assert flag in b and flag in mk, flag
     for src in re.findall(r"\$\(CS\)/(host_[a-z_]+)\.o:", mk):
         assert f'"{src}"' in b, src
+
+
+def test_reference_patch_only_uses_symbols_the_sys_crate_defines():
+    """rust/reference-patch/*.rs (flatten(), render() over mp_render) name nothing in `sys::` that lib.rs does not declare,
+    and every struct literal they build names exactly the struct's fields."""
+    lib = _strip_rs(open(LIB_RS).read())
+    defined = set(re.findall(r"pub (?:fn|struct|const|type) ([A-Za-z_0-9]+)", lib))
+    structs = rust_structs()
+    patch_dir = os.path.join(ROOT, "rust", "reference-patch")
+    used = set()
+    for name in sorted(os.listdir(patch_dir)):
+        text = _strip_rs(open(os.path.join(patch_dir, name)).read())
+        used |= set(re.findall(r"\bsys::([A-Za-z_0-9]+)", text))
+        for m in re.finditer(r"sys::(Mp[A-Za-z0-9]+) \{(.*?)\n\s*\}", text, flags=re.S):
+            body = m.group(2)
+            if ".." in body:  # ..Default::default()
+                continue
+            depth, top = 0, ""
+            for ch in body:  # keep only the literal's own nesting level
+                if ch in "([{":
+                    depth += 1
+                elif ch in ")]}":
+                    depth -= 1
+                elif depth == 0:
+                    top += ch
+            fields = re.findall(r"(?:^|,)\s*([a-z_0-9]+)\s*(?::|,|$)", top, flags=re.M)
+            want = [f for f, _ in structs[m.group(1)]]
+            assert sorted(set(fields)) == sorted(want), (name, m.group(1), fields, want)
+    assert used and used <= defined, sorted(used - defined)
