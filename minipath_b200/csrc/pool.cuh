@@ -22,7 +22,18 @@ namespace mpd {
 #define POOL_W 96       // ray slots per warp
 #endif
 #define POOL_RING 128   // ring capacity (power of two >= POOL_W)
+#ifndef POOL_VEC_RAY
+#define POOL_VEC_RAY 0  // 1: the read-only part of a slot (origin, direction, inv.xy) lives in two float4 groups read with LDS.128 — a 128-bit warp access
+                        // is served per quarter-warp, so the bank conflicts of arbitrary slot sets arise among 8 lanes instead of 32, and 8 scalar loads become 2
+#endif
+#if POOL_VEC_RAY
+#define POOL_VECS 2     // float4 groups per slot
+#define POOL_COLS 13    // 4-byte state columns per slot
+#else
+#define POOL_VECS 0
 #define POOL_COLS 21    // 4-byte state columns per slot
+#endif
+#define POOL_STATE_BYTES ((POOL_VECS * 16 + POOL_COLS * 4) * POOL_W)  // per warp; 84 bytes per slot either way
 #define POOL_WARPS 4    // warps per block
 #ifndef POOL_MIN_BLOCKS
 #define POOL_MIN_BLOCKS 5  // resident blocks per SM the register allocation aims at; measured: 6 (80 regs) and 8 (64 regs, 64-ray pools) are 3-15 % slower
@@ -37,16 +48,21 @@ namespace mpd {
                         // Measured on the stand-in (8 spp, ms per frame): 0 -> 79.4, 2 -> 85.8, 4 -> 86.7: the ring bookkeeping in the unrolled
                         // child loop and the lost occupancy cost more than the L1 requests it saves, so it is off.
 #endif
-#define POOL_SMEM_PER_WARP (POOL_COLS * POOL_W * 4 + 3 * POOL_RING + POOL_SS * POOL_W * 8)
+#define POOL_SMEM_PER_WARP (POOL_STATE_BYTES + 3 * POOL_RING + POOL_SS * POOL_W * 8)
 
 struct PoolWarp {  // shared-memory view of one warp's pool
+    float4* vec;         // [POOL_VECS][POOL_W]  (POOL_VEC_RAY)
     float* col;          // [POOL_COLS][POOL_W]
     unsigned char* ring; // [3][POOL_RING]: 0 inner items, 1 packet items, 2 free slots
     __device__ __forceinline__ float& f(int c, uint32_t s) const { return col[c * POOL_W + s]; }
     __device__ __forceinline__ uint32_t& u(int c, uint32_t s) const { return reinterpret_cast<uint32_t*>(col)[c * POOL_W + s]; }
 };
 // columns
-enum { PC_OX, PC_OY, PC_OZ, PC_DX, PC_DY, PC_DZ, PC_IX, PC_IY, PC_IZ, PC_BT, PC_BU, PC_BV, PC_BTRI, PC_SP, PC_RID, PC_PIDX, PC_REM,
+enum {
+#if !POOL_VEC_RAY
+       PC_OX, PC_OY, PC_OZ, PC_DX, PC_DY, PC_DZ, PC_IX, PC_IY,
+#endif
+       PC_IZ, PC_BT, PC_BU, PC_BV, PC_BTRI, PC_SP, PC_RID, PC_PIDX, PC_REM,
        PC_LT, PC_LU, PC_LV, PC_LTRI };
 
 // Per-ray traversal stack.  Profiling the first pool kernel showed three quarters of its global L1 requests were stack pushes and
@@ -175,10 +191,28 @@ __device__ __forceinline__ void pool_advance(const PoolWarp& pw, PoolQueues& qs,
 
 __device__ __forceinline__ Ray pool_load_ray(const PoolWarp& pw, uint32_t s) {
     Ray r;
+#if POOL_VEC_RAY
+    const float4 a = pw.vec[s], b = pw.vec[POOL_W + s];
+    r.o = f3(a.x, a.y, a.z);
+    r.d = f3(a.w, b.x, b.y);
+    r.inv = f3(b.z, b.w, pw.f(PC_IZ, s));
+#else
     r.o = f3(pw.f(PC_OX, s), pw.f(PC_OY, s), pw.f(PC_OZ, s));
     r.d = f3(pw.f(PC_DX, s), pw.f(PC_DY, s), pw.f(PC_DZ, s));
     r.inv = f3(pw.f(PC_IX, s), pw.f(PC_IY, s), pw.f(PC_IZ, s));
+#endif
     return r;
+}
+__device__ __forceinline__ void pool_store_ray(const PoolWarp& pw, uint32_t s, const Ray& r) {
+#if POOL_VEC_RAY
+    pw.vec[s] = make_float4(r.o.x, r.o.y, r.o.z, r.d.x);
+    pw.vec[POOL_W + s] = make_float4(r.d.y, r.d.z, r.inv.x, r.inv.y);
+    pw.f(PC_IZ, s) = r.inv.z;
+#else
+    pw.f(PC_OX, s) = r.o.x, pw.f(PC_OY, s) = r.o.y, pw.f(PC_OZ, s) = r.o.z;
+    pw.f(PC_DX, s) = r.d.x, pw.f(PC_DY, s) = r.d.y, pw.f(PC_DZ, s) = r.d.z;
+    pw.f(PC_IX, s) = r.inv.x, pw.f(PC_IY, s) = r.inv.y, pw.f(PC_IZ, s) = r.inv.z;
+#endif
 }
 
 // fetch(i, r) loads ray i completely (o, d, inv); emit(i, hit) stores its result.  `claim` is a zeroed device counter shared by
@@ -189,10 +223,11 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
     constexpr uint32_t FULL = 0xffffffffu;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     PoolWarp pw;
-    pw.col = reinterpret_cast<float*>(smem + (size_t)warp * POOL_SMEM_PER_WARP);
-    pw.ring = smem + (size_t)warp * POOL_SMEM_PER_WARP + POOL_COLS * POOL_W * 4;
+    pw.vec = reinterpret_cast<float4*>(smem + (size_t)warp * POOL_SMEM_PER_WARP);
+    pw.col = reinterpret_cast<float*>(smem + (size_t)warp * POOL_SMEM_PER_WARP + POOL_VECS * 16 * POOL_W);
+    pw.ring = smem + (size_t)warp * POOL_SMEM_PER_WARP + POOL_STATE_BYTES;
     uint2* const wstacks = scratch + ((size_t)blockIdx.x * POOL_WARPS + warp) * POOL_W * stack_cap;
-    uint2* const wring = reinterpret_cast<uint2*>(smem + (size_t)warp * POOL_SMEM_PER_WARP + POOL_COLS * POOL_W * 4 + 3 * POOL_RING);
+    uint2* const wring = reinterpret_cast<uint2*>(smem + (size_t)warp * POOL_SMEM_PER_WARP + POOL_STATE_BYTES + 3 * POOL_RING);
     constexpr bool SHORT = ORDER == MP_ORDER_REFERENCE && POOL_SS > 0;
     using Stack = PStack<SHORT>;
     PoolQueues qs{};
@@ -217,9 +252,7 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
                 slot = pw.ring[2 * POOL_RING + ((qs.head[2] + lane) & (POOL_RING - 1))];
                 Ray r;
                 fetch(base + lane, r);
-                pw.f(PC_OX, slot) = r.o.x, pw.f(PC_OY, slot) = r.o.y, pw.f(PC_OZ, slot) = r.o.z;
-                pw.f(PC_DX, slot) = r.d.x, pw.f(PC_DY, slot) = r.d.y, pw.f(PC_DZ, slot) = r.d.z;
-                pw.f(PC_IX, slot) = r.inv.x, pw.f(PC_IY, slot) = r.inv.y, pw.f(PC_IZ, slot) = r.inv.z;
+                pool_store_ray(pw, slot, r);
                 pw.f(PC_BT, slot) = MPD_FLT_MAX, pw.f(PC_BU, slot) = 0.0f, pw.f(PC_BV, slot) = 0.0f, pw.u(PC_BTRI, slot) = MP_NO_HIT;
                 pw.u(PC_RID, slot) = base + lane;
                 tc.rays++;
@@ -329,7 +362,8 @@ __device__ __forceinline__ void pool_run_owned(const Scene& sc, uint32_t n, uint
     static_assert(POOL_W % 32 == 0 && K <= 8, "lane-owned pools hold a whole number of slots per lane");
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     PoolWarp pw;
-    pw.col = reinterpret_cast<float*>(smem + (size_t)warp * POOL_SMEM_PER_WARP);
+    pw.vec = reinterpret_cast<float4*>(smem + (size_t)warp * POOL_SMEM_PER_WARP);
+    pw.col = reinterpret_cast<float*>(smem + (size_t)warp * POOL_SMEM_PER_WARP + POOL_VECS * 16 * POOL_W);
     pw.ring = nullptr;
     uint2* const wstacks = scratch + ((size_t)blockIdx.x * POOL_WARPS + warp) * POOL_W * stack_cap;
     using Stack = PStack<false>;
@@ -366,9 +400,7 @@ __device__ __forceinline__ void pool_run_owned(const Scene& sc, uint32_t n, uint
                     const uint32_t slot = (uint32_t)k * 32u + lane;
                     Ray r;
                     fetch(idx, r);
-                    pw.f(PC_OX, slot) = r.o.x, pw.f(PC_OY, slot) = r.o.y, pw.f(PC_OZ, slot) = r.o.z;
-                    pw.f(PC_DX, slot) = r.d.x, pw.f(PC_DY, slot) = r.d.y, pw.f(PC_DZ, slot) = r.d.z;
-                    pw.f(PC_IX, slot) = r.inv.x, pw.f(PC_IY, slot) = r.inv.y, pw.f(PC_IZ, slot) = r.inv.z;
+                    pool_store_ray(pw, slot, r);
                     pw.f(PC_BT, slot) = MPD_FLT_MAX, pw.f(PC_BU, slot) = 0.0f, pw.f(PC_BV, slot) = 0.0f, pw.u(PC_BTRI, slot) = MP_NO_HIT;
                     pw.u(PC_RID, slot) = idx;
                     tc.rays++;
