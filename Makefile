@@ -19,11 +19,14 @@ $(CS)/host_render.o: $(CS)/host_render.cpp $(CS)/host_common.h include/minipath_
 	$(CXX) $(HOST_FLAGS) -c $< -o $@
 $(CS)/host_image.o: $(CS)/host_image.cpp $(CS)/host_common.h include/minipath_b200.h
 	$(CXX) $(HOST_FLAGS) -c $< -o $@
+$(CS)/host_group.o: $(CS)/host_group.cpp $(CS)/host_common.h include/minipath_b200.h
+	$(CXX) $(HOST_FLAGS) -I/usr/local/cuda/include -c $< -o $@
 $(CS)/context.o: $(CS)/context.cu $(CS)/context_render.inc $(CS)/context_probes.inc $(CS)/probes.cuh $(CS)/octet.cuh $(CS)/persist.cuh $(CS)/pool.cuh $(CS)/decode.cuh $(CS)/kernels.cuh $(CS)/wavefront.cuh $(CS)/trace.cuh $(CS)/device_math.cuh include/minipath_b200.h
 	$(NVCC) $(NVCC_FLAGS) -c $< -o $@ 2> $(CS)/ptxas.log || (cat $(CS)/ptxas.log; false)
 
-$(LIB): $(CS)/host_bvh.o $(CS)/host_camera.o $(CS)/host_render.o $(CS)/host_image.o $(CS)/context.o
-	$(NVCC) -shared -o $@ $^ -lpthread -lrt -cudart static
+HOST_OBJS := $(CS)/host_bvh.o $(CS)/host_camera.o $(CS)/host_render.o $(CS)/host_image.o $(CS)/host_group.o
+$(LIB): $(HOST_OBJS) $(CS)/context.o
+	$(NVCC) -shared -o $@ $^ -lpthread -lrt -ldl -cudart static
 
 $(ORACLE): oracle/oracle.cpp oracle/oracle_trace.inc oracle/oracle_render.inc oracle/oracle.h include/minipath_b200.h
 	$(CXX) -O2 -std=c++17 -fPIC -shared -mavx2 -mfma -ffp-contract=off -Wall -o $@ oracle/oracle.cpp -lpthread

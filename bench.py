@@ -4,17 +4,23 @@
     python bench.py --gpus N --steps K --warmup W                  # this repo's CUDA path
     python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's CPU path (oracle port) on host cores
 
-One step = one full frame of the workload (all screen tiles, all samples).  Metric (BASELINE.json): Mrays/s
-(all ray segments: camera + bounce + shadow) with samples/s beside it.  Prints ONE JSON line on rank 0.
+One step = one full frame of the workload (all screen tiles, all samples).  Metric (BASELINE.json): Mrays/s (all ray
+segments: camera + bounce + shadow) with samples/s beside it.  Prints ONE JSON line on rank 0.
 
-  value        device-resident: scene, camera and tiles already in HBM; CUDA events around each step on the launching stream
-  e2e          the same frame through the reference-facing call `minipath_b200.render()` (mp_render: host scene arrays →
-               device, tiles rendered, RGBA8 image back in host memory), host<->device copies inside the timed region
-  roofline     dominant kernel against the measured FP32 / L2 / HBM denominators
+Default workload = the north_star target, BASELINE configs[2]: the Sponza STAND-IN ("atrium", sponza.obj is absent from the
+reference) at 1920x1080, 256 spp, 5 bounces.  configs[1] (teapot 1920x1080, 64 spp, 5 bounces) rides along as `extra` at N=1.
+
+  value        device-resident: scene, camera and tiles already in HBM; CUDA events around each step on the launching stream,
+               the pipeline MP_MODE_AUTO picks (what render() runs)
+  e2e          the same frame through the reference-facing API with HOST buffers: N=1 `minipath_b200.render()` + wait() + image()
+               (mp_render); N>1 the mp_group_* C ABI (scene upload from host arrays, dynamic tile queue, NCCL film reduce inside
+               the library, RGBA8 image back on the host of rank 0)
+  roofline     whole step against the measured FP32 / L2 / L1-gather / HBM denominators, SURVEY §8(d) constants
   cpu_baseline the oracle (CPU restatement of the reference path; `kind: port`) on the box's host cores, bounded sample
 
-Multi-GPU (torchrun, one rank per GPU): samples are split over ranks (`sample_base`), films summed by one NCCL reduce
-to rank 0; per-GPU work is fixed as N grows ("weak").
+Multi-GPU (torchrun, one rank per GPU): tile sharding — the ranks pull batches of tiles from ONE shared counter (the
+reference's scheduler, machinery.rs:205-209), total work fixed ("strong"), films combined by one ncclReduce inside the
+library.  `--shard spp` splits the samples instead (configs[3], "weak": per-GPU work fixed).
 """
 import argparse
 import json
@@ -31,13 +37,29 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
-# algorithmic work per visit: bytes fetched and f32 arithmetic of the reference algorithm
-BYTES_INNER = 128 + 32   # node (6 x u16x8 + 8 links) + its enclosing box (min,size)
+# Algorithmic work per visit — SURVEY §8(d): bytes/ray = 128 n_inner + 144 n_pack + 36 (ray in) + 16 (hit out) + 24 (n_inner +
+# n_leaf) for the stored per-node boxes; flops/ray = 390 n_inner + 620 n_pack.
+BYTES_INNER = 128        # 6 x u16x8 child bounds + 8 links
 BYTES_PACKET = 144       # 9 x u16x8
-BYTES_LEAF = 32          # enclosing box of the leaf
+BYTES_BOX = 24           # enclosing box (min, size) of an inner node / a leaf, stored on the device
 BYTES_RAY = 36 + 16      # ray in, hit out
-FLOPS_INNER = 8 * 48     # per child: 6 dequant (cvt+mul+fma=4) + 6 sub + 6 mul + 12 min/max
-FLOPS_PACKET = 8 * 87    # per triangle: 9 dequant (36) + Moller-Trumbore (51: 6 sub, 2 cross, 4 dot, 3 mul, 3 sub, 1 div)
+FLOPS_INNER = 390
+FLOPS_PACKET = 620
+# what the device records actually hold per visit (round 1's constants; printed beside the above as `alt`): 160-byte node record,
+# 144-byte packet + 32-byte leaf box; 8 x 48 flop per node, 8 x 87 per packet counted from the SASS
+ALT = dict(BYTES_INNER=160, BYTES_PACKET=144, BYTES_LEAF=32, BYTES_RAY=52, FLOPS_INNER=384, FLOPS_PACKET=696)
+
+# name -> (scene, width, height, spp, max_bounces); BASELINE.json configs
+WORKLOADS = {
+    "atrium-1080p": ("atrium", 1920, 1080, 256, 5),    # configs[2] on the procedural Sponza stand-in: the north_star target
+    "teapot-1080p": ("teapot", 1920, 1080, 64, 5),     # configs[1]: teapot 1920x1080, 64 spp, 5 bounces
+    "cube-1080p": ("cube", 1920, 1080, 64, 5),         # configs[1], the cube half
+    "teapot-bench": ("teapot", 2048, 1536, 10, 0),     # configs[0]: benches/render_teapot.rs:12-24 (reference shader)
+    "atrium-4k": ("atrium", 3840, 2160, 1024, 8),      # configs[3] on the stand-in: spp split over the GPUs, NCCL film reduce
+}
+DEFAULT_WORKLOAD = "atrium-1080p"
+PIPELINES = ["megakernel", "wavefront-octet", "wavefront-thread", "wavefront-persist", "wavefront-hybrid", "wavefront-pool",
+             "wavefront-hybrid-pool", "wavefront-hybrid-pool-s0"]
 
 
 def parse_args():
@@ -46,31 +68,22 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="teapot-1080p", choices=sorted(WORKLOADS))
-    ap.add_argument("--mode", default="auto", choices=["auto", "megakernel", "wavefront-octet", "wavefront-thread", "wavefront-persist", "wavefront-hybrid", "wavefront-pool",
-                                                     "wavefront-hybrid-pool", "wavefront-hybrid-pool-s0"],
-                    help="megakernel: one thread per pixel; wavefront-*: staged kernels with the thread-per-ray, the 8-lanes-per-ray "
-                         "(octet) or the persistent phased thread-per-ray traversal kernel")
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--mode", default="auto", choices=["auto"] + PIPELINES,
+                    help="auto: the pipeline MP_MODE_AUTO / render() picks; otherwise force one (A/B runs)")
+    ap.add_argument("--ab", action="store_true", help="also time every pipeline once (1 warm-up + 1 step each) and report it in `pipeline_ab_ms`")
     ap.add_argument("--order", default="reference", choices=["reference", "near_first"])
-    ap.add_argument("--layout", default="auto", choices=["auto", "decoded", "quantised"],
-                    help="node layout read by the traversal kernels: f32 boxes/edges decoded at upload (default) or the reference's u16 records")
+    ap.add_argument("--layout", default="auto", choices=["auto", "decoded", "quantised"])
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel")
     ap.add_argument("--bounces", type=int, default=-1, help="override the workload's max_bounces")
-    ap.add_argument("--shard", default="spp", choices=["spp", "tiles"])
+    ap.add_argument("--shard", default="tiles", choices=["tiles", "spp"], help="N>1: dynamic tile queue (strong scaling) or sample split (weak)")
+    ap.add_argument("--min-batch", type=int, default=4, help="N>1 tile sharding: smallest batch of tiles a GPU claims")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--ref-spp", type=int, default=16, help="--impl reference: samples per pixel of one bounded step")
+    ap.add_argument("--no-extra", action="store_true", help="skip the teapot-1080p (configs[1]) rider")
+    ap.add_argument("--ref-seconds", type=float, default=12.0, help="CPU arms: target seconds of oracle work per bounded step")
+    ap.add_argument("--timeline", default="", help="N>1: write a per-rank timeline of one step (JSON) to this path")
     return ap.parse_args()
-
-
-# name -> (scene, width, height, spp, max_bounces); BASELINE.json configs
-WORKLOADS = {
-    "teapot-1080p": ("teapot", 1920, 1080, 64, 5),     # configs[1]: teapot 1920x1080, 64 spp, 5 bounces
-    "cube-1080p": ("cube", 1920, 1080, 64, 5),         # configs[1], the cube half
-    "teapot-bench": ("teapot", 2048, 1536, 10, 0),     # configs[0]: benches/render_teapot.rs:12-24 (reference shader)
-    "atrium-1080p": ("atrium", 1920, 1080, 256, 5),    # configs[2] on the procedural Sponza stand-in (sponza.obj is absent)
-    "atrium-4k": ("atrium", 3840, 2160, 1024, 8),      # configs[3] on the stand-in: spp split over the GPUs, NCCL film reduce
-}
 
 
 class ClockSampler(threading.Thread):
@@ -105,16 +118,22 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows)}
 
 
+def workload_params(name, args):
+    scene, w, h, spp, bounces = WORKLOADS[name]
+    if name == args.workload:
+        if args.spp > 0:
+            spp = args.spp
+        if args.bounces >= 0:
+            bounces = args.bounces
+    return scene, w, h, spp, bounces
+
+
 def load_workload(name, args):
     """Scene (host BVH), camera and frame parameters of a workload.  Built on the host, outside every timed region
     (benches/render_teapot.rs:25-27 excludes the scene build too)."""
     import minipath_b200 as mp
 
-    scene, w, h, spp, bounces = WORKLOADS[name]
-    if args.spp > 0:
-        spp = args.spp
-    if args.bounces >= 0:
-        bounces = args.bounces
+    scene, w, h, spp, bounces = workload_params(name, args)
     data = os.path.join(ROOT, "data")
     if scene == "teapot":  # camera of benches/render_teapot.rs:12-19
         bvh = mp.TriangleBvh.with_obj(os.path.join(data, "teapot.obj"))
@@ -129,6 +148,21 @@ def load_workload(name, args):
     return bvh, cam, w, h, spp, bounces
 
 
+def workload_config(name, args):
+    """The `config` object both arms print: identical keys and values for the CUDA arm and the reference arm."""
+    scene, w, h, spp, bounces = workload_params(name, args)
+    return {"workload": name, "scene": scene + (" (procedural Sponza STAND-IN; sponza.obj is absent from the reference)" if scene == "atrium" else ".obj of the reference"),
+            "resolution": [w, h], "spp": spp, "max_bounces": bounces, "tile_size": 64,
+            "l2": "flushed between timed steps (256 MB fill outside the event pairs); inputs resident in HBM",
+            "note": "max_bounces>0 is the extension integrator (the reference traces primary rays only)"}
+
+
+def data_note(name):
+    scene = WORKLOADS[name][0]
+    return "synthetic camera samples (counter-based RNG) on " + ("the reference's data/%s.obj" % scene if scene != "atrium" else
+                                                                 "a procedural Sponza STAND-IN (sponza.obj is absent from the reference)")
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -136,6 +170,9 @@ def host_cores():
         return os.cpu_count() or 1
 
 
+# ------------------------------------------------------------------------------------------------------------------
+# CPU arms (the oracle is test infrastructure: it runs ONLY here, as the thing beside the measurement, never inside it)
+# ------------------------------------------------------------------------------------------------------------------
 def oracle_frame(oracle, bvh, sampler, w, h, tiles, params, threads):
     """One bounded frame on the CPU oracle; returns (seconds, rays, camera samples)."""
     from minipath_b200 import _ffi
@@ -145,9 +182,18 @@ def oracle_frame(oracle, bvh, sampler, w, h, tiles, params, threads):
     return secs, int(c.rays), int(c.camera_rays)
 
 
+def bounded_spp(oracle, bvh, sampler, w, h, tiles, bounces, spp, threads, seconds):
+    """How many of the workload's spp fit `seconds` of oracle work (calibrated with one 1-spp frame)."""
+    import minipath_b200 as mp
+
+    st1 = mp.RenderSettings(64, 1, (w, h), max_bounces=bounces, seed=7)
+    s1, _, _ = oracle_frame(oracle, bvh, sampler, w, h, tiles, st1.params(), threads)
+    return int(max(1, min(spp, round(seconds / max(s1, 1e-3)))))
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU path (oracle port — the Rust crate cannot be built here) on all host
-    cores, same workload/metric; each step is a bounded sample (ref_spp samples per pixel of the full frame)."""
+    """--impl reference: the reference's CPU path (oracle port — the Rust crate cannot be built here) on all host cores, same
+    workload, metric and config object; each step is a bounded sample: the full frame at `sample_spp` of the workload's spp."""
     if rank != 0:
         return
     import minipath_b200 as mp
@@ -159,22 +205,23 @@ def run_reference(args, rank, world):
     threads = host_cores()
     sampler = cam.build_sampler((w, h))
     tiles = mp.full_screen_tiles(w, h, 64)
-    st = mp.RenderSettings(64, args.ref_spp, (w, h), max_bounces=bounces, seed=7)
-    for _ in range(args.warmup):
+    n = bounded_spp(oracle, bvh, sampler, w, h, tiles, bounces, spp, threads, args.ref_seconds)
+    st = mp.RenderSettings(64, n, (w, h), max_bounces=bounces, seed=7)
+    for _ in range(min(args.warmup, 1)):  # the calibration frame has already warmed caches and threads
         oracle_frame(oracle, bvh, sampler, w, h, tiles, st.params(), threads)
     secs = rays = samples = 0
     for _ in range(args.steps):
         s, r, c = oracle_frame(oracle, bvh, sampler, w, h, tiles, st.params(), threads)
         secs, rays, samples = secs + s, rays + r, samples + c
     mrays = rays / secs / 1e6
-    sample = f"{args.workload}: full {w}x{h} frame at {args.ref_spp} of {spp} spp per step, {bounces} bounces"
+    sample = f"{args.workload}: full {w}x{h} frame at {n} of {spp} spp per step, {bounces} bounces, AVX2+FMA oracle, {threads} threads"
     line = {
         "impl": "reference", "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic camera samples on data/teapot.obj" if "teapot" in args.workload else "synthetic",
-        "samples_per_s": samples / secs,
-        "config": {"workload": args.workload, "resolution": [w, h], "spp": spp, "max_bounces": bounces, "tile_size": 64,
-                   "note": "CPU restatement of the reference path (oracle port; cargo/rustc absent), AVX2+FMA lanes, thread per core"},
+        "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "strong" if args.shard == "tiles" else "weak", "vs_baseline": None, "dtype": "f32", "data": data_note(args.workload),
+        "samples_per_s": samples / secs, "config": workload_config(args.workload, args),
+        "sample": sample, "sample_spp": n,
+        "reference_kind": "CPU restatement of the reference path (oracle port; cargo/rustc absent), thread per core, atomic tile queue",
         "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -182,7 +229,7 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def cpu_baseline(args, bvh, cam, w, h, spp, bounces):
+def cpu_baseline(args, name, bvh, cam, w, h, spp, bounces):
     """Oracle on the host cores, bounded to roughly 10-20 s: 1 spp to calibrate, then as many spp as fit."""
     import minipath_b200 as mp
     from oracle_lib import Oracle
@@ -192,121 +239,96 @@ def cpu_baseline(args, bvh, cam, w, h, spp, bounces):
     threads = host_cores()
     sampler = cam.build_sampler((w, h))
     tiles = mp.full_screen_tiles(w, h, 64)
-    st1 = mp.RenderSettings(64, 1, (w, h), max_bounces=bounces, seed=7)
-    s1, _, _ = oracle_frame(oracle, bvh, sampler, w, h, tiles, st1.params(), threads)
-    n = int(max(1, min(spp, round(12.0 / max(s1, 1e-3)))))
+    n = bounded_spp(oracle, bvh, sampler, w, h, tiles, bounces, spp, threads, args.ref_seconds)
     st = mp.RenderSettings(64, n, (w, h), max_bounces=bounces, seed=7)
     secs, rays, samples = oracle_frame(oracle, bvh, sampler, w, h, tiles, st.params(), threads)
     return {"value": rays / secs / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port", "samples_per_s": samples / secs,
-            "seconds": secs, "sample": f"{args.workload}: full {w}x{h} frame at {n} of {spp} spp, {bounces} bounces, AVX2 oracle"}
+            "seconds": secs, "sample": f"{name}: full {w}x{h} frame at {n} of {spp} spp, {bounces} bounces, AVX2+FMA oracle, {threads} threads"}
 
 
-def init_dist(args):
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    return rank, local, world
-
-
-def run_b200(args, rank, local, world):
-    import torch
-    import torch.distributed as dist
-
-    import minipath_b200 as mp
-    from minipath_b200 import dist as mpdist
-
-    if not torch.cuda.is_available() or mp.device_count() == 0:
-        raise SystemExit("bench.py: no CUDA device — the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    bvh, cam, w, h, spp, bounces = load_workload(args.workload, args)
-    order = mp.ORDER_REFERENCE if args.order == "reference" else mp.ORDER_NEAR_FIRST
-    sampler = cam.build_sampler((w, h))
-    tiles = mp.full_screen_tiles(w, h, 64)
-
-    stream = torch.cuda.Stream()
-    ctx = mp.Context(local)
-    ctx.set_stream(stream.cuda_stream)
-    ctx.set_node_layout({"auto": mp.LAYOUT_AUTO, "decoded": mp.LAYOUT_DECODED, "quantised": mp.LAYOUT_QUANTISED}[args.layout])
-    ctx.upload_scene(bvh)
-    ctx.set_camera(sampler)
-    film = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
-    ctx.bind_film(film.data_ptr(), w, h)
-    rgba = torch.empty((h, w), dtype=torch.int32, device="cuda")
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
-
-    def reduce_fn(t):
-        dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
-
-    modes = {"megakernel": mp.MODE_MEGAKERNEL, "wavefront-thread": mp.MODE_WAVEFRONT, "wavefront-octet": mp.MODE_WAVEFRONT,
-             "wavefront-persist": mp.MODE_WAVEFRONT, "wavefront-hybrid": mp.MODE_WAVEFRONT,
-             "wavefront-pool": mp.MODE_WAVEFRONT, "wavefront-hybrid-pool": mp.MODE_WAVEFRONT,
-             "wavefront-hybrid-pool-s0": mp.MODE_WAVEFRONT}
+# ------------------------------------------------------------------------------------------------------------------
+# CUDA arm
+# ------------------------------------------------------------------------------------------------------------------
+def pipeline_tables(mp):
+    modes = {k: (mp.MODE_MEGAKERNEL if k == "megakernel" else mp.MODE_WAVEFRONT) for k in PIPELINES}
     variants = {"megakernel": mp.TRACE_THREAD, "wavefront-thread": mp.TRACE_THREAD, "wavefront-octet": mp.TRACE_OCTET,
-                "wavefront-persist": mp.TRACE_PERSIST, "wavefront-hybrid": mp.TRACE_HYBRID,
-                "wavefront-pool": mp.TRACE_POOL, "wavefront-hybrid-pool": mp.TRACE_HYBRID_POOL,
-                "wavefront-hybrid-pool-s0": mp.TRACE_HYBRID_POOL_S0}
-    if bvh.stats()["max_stack"] > 128:  # deeper than the local-memory stack of the thread-per-ray kernels
-        modes = {"wavefront-octet": mp.MODE_WAVEFRONT, "wavefront-pool": mp.MODE_WAVEFRONT}
+                "wavefront-persist": mp.TRACE_PERSIST, "wavefront-hybrid": mp.TRACE_HYBRID, "wavefront-pool": mp.TRACE_POOL,
+                "wavefront-hybrid-pool": mp.TRACE_HYBRID_POOL, "wavefront-hybrid-pool-s0": mp.TRACE_HYBRID_POOL_S0}
+    return modes, variants
 
-    def make_step(mode_key):
-        mode = modes[mode_key]
 
-        def render_fn(sub_tiles, base, count):
-            st = mp.RenderSettings(64, count, (w, h), max_bounces=bounces, seed=7, mode=mode, order=order)
-            ctx.render_tiles(sub_tiles, st.params(sample_base=base))
+def auto_pipeline(bvh, bounces):
+    """The pick of MP_MODE_AUTO (minipath_b200/csrc/host_render.cpp: mp_render), so that `value` times what render() runs."""
+    st = bvh.stats()
+    deep = st["max_stack"] > 128
+    if not deep and (bounces == 0 or st["n_inner"] == 0):
+        return "megakernel"
+    return "wavefront-pool" if deep else "wavefront-hybrid-pool-s0"
 
-        def step():
-            ctx.set_trace_variant(variants[mode_key])
-            film.zero_()
-            # weak scaling: every rank renders the full frame with its own `spp` sample indices; total spp = spp * world
-            mpdist.render_sharded(render_fn, film, tiles, spp * world if args.shard == "spp" else spp, rank, world, args.shard,
-                                  reduce_fn=reduce_fn if world > 1 else None)
-            if rank == 0:
-                ctx.resolve_device(spp * world if args.shard == "spp" else spp, rgba.data_ptr())
-        return step
 
-    def timed(step, n_warm, n_steps):
-        """Per-step CUDA events on the launching stream, L2 flushed between steps (outside the event pairs)."""
+class Timer:
+    """Per-step CUDA events on the launching stream, L2 flushed between steps (outside the event pairs)."""
+
+    def __init__(self, torch, stream):
+        self.torch, self.stream = torch, stream
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def run(self, step, n_warm, n_steps):
+        torch, stream = self.torch, self.stream
         with torch.cuda.stream(stream):
             for _ in range(n_warm):
                 step()
             evs = []
             for _ in range(n_steps):
-                flush.fill_(1)
+                self.flush.fill_(1)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(stream)
                 step()
                 e1.record(stream)
                 evs.append((e0, e1))
             stream.synchronize()
-        return sum(a.elapsed_time(b) for a, b in evs)
+        return [a.elapsed_time(b) for a, b in evs]
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
 
-    # ---- pick the pipeline: the A/B the north_star asks for, measured here, reported in config ----
+def measure_single(args, name, torch, local, full=True):
+    """N = 1: device-resident `value` through a Context, `e2e` through minipath_b200.render()."""
+    import minipath_b200 as mp
+
+    bvh, cam, w, h, spp, bounces = load_workload(name, args)
+    order = mp.ORDER_REFERENCE if args.order == "reference" else mp.ORDER_NEAR_FIRST
+    sampler = cam.build_sampler((w, h))
+    tiles = mp.full_screen_tiles(w, h, 64)
+    modes, variants = pipeline_tables(mp)
+    if bvh.stats()["max_stack"] > 128:  # deeper than the local-memory stack of the thread-per-ray kernels
+        modes = {k: v for k, v in modes.items() if k in ("wavefront-octet", "wavefront-pool")}
+    stream = torch.cuda.Stream()
+    ctx = mp.Context(local)
+    ctx.set_stream(stream.cuda_stream)
+    ctx.set_node_layout({"auto": mp.LAYOUT_AUTO, "decoded": mp.LAYOUT_DECODED, "quantised": mp.LAYOUT_QUANTISED}[args.layout])
+    ctx.upload_scene(bvh)
+    ctx.set_camera(sampler)
+    ctx.create_film(w, h)
+    rgba = torch.empty((h, w), dtype=torch.int32, device="cuda")
+    timer = Timer(torch, stream)
+
+    def make_step(key):
+        st = mp.RenderSettings(64, spp, (w, h), max_bounces=bounces, seed=7, mode=modes[key], order=order)
+
+        def step():
+            ctx.set_trace_variant(variants[key])
+            ctx.clear_film()
+            ctx.render_tiles(tiles, st.params())
+            ctx.resolve_device(spp, rgba.data_ptr())
+        return step
+
+    mode_name = auto_pipeline(bvh, bounces) if (args.mode == "auto" or name != args.workload) else args.mode
     ab = {}
-    if args.mode == "auto":
-        for name in modes:
-            barrier()
-            ab[name] = timed(make_step(name), 1, 1)
-        if world > 1:
-            t = torch.tensor([ab[k] for k in modes], device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ab = {k: float(t[i]) for i, k in enumerate(modes)}
-        mode_name = min(ab, key=ab.get)
-    else:
-        mode_name = args.mode
+    if args.ab and full:
+        for key in modes:
+            ab[key] = sum(timer.run(make_step(key), 1, 1))
     step = make_step(mode_name)
 
-    # ---- counted pass (untimed): rays and node visits of one step, deterministic for a given seed ----
+    # counted pass (untimed): rays and node visits of one step, deterministic for a given seed
     ctx.enable_counters(True)
     ctx.reset_counters()
     with torch.cuda.stream(stream):
@@ -315,187 +337,333 @@ def run_b200(args, rank, local, world):
     cnt = ctx.counters()
     ctx.enable_counters(False)
 
-    # ---- timed region ----
-    sampler_thread = ClockSampler(local) if rank == 0 else None
-    with torch.cuda.stream(stream):
-        for _ in range(args.warmup):
-            step()
+    sampler_thread = ClockSampler(local) if full else None
+    timer.run(step, args.warmup, 0)
     ctx.reset_counters()
-    barrier()
+    torch.cuda.synchronize()
     if sampler_thread:
         sampler_thread.start()
-    total_ms = timed(step, 0, args.steps)
-    barrier()
+    per_step = timer.run(step, 0, args.steps)
+    torch.cuda.synchronize()
     clocks = sampler_thread.stop() if sampler_thread else None
     launches = ctx.counters()["launches"]
-    if world > 1:
-        t = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t[0])
-        r = torch.tensor([cnt["rays"], cnt["camera_rays"]], device="cuda", dtype=torch.float64)
-        dist.all_reduce(r, op=dist.ReduceOp.SUM)
-        rays_job, samples_job = float(r[0]), float(r[1])
-    else:
-        rays_job, samples_job = float(cnt["rays"]), float(cnt["camera_rays"])
-    ms_per_step = total_ms / args.steps
-    value = rays_job / (ms_per_step * 1e-3) / 1e6
+    ms_per_step = sum(per_step) / args.steps
+    res = dict(name=name, ctx=ctx, bvh=bvh, cam=cam, w=w, h=h, spp=spp, bounces=bounces, tiles=tiles, cnt=cnt, ab=ab, mode_name=mode_name,
+               ms_per_step=ms_per_step, per_step_ms=per_step, value=cnt["rays"] / (ms_per_step * 1e-3) / 1e6, world=1,
+               samples_per_s=cnt["camera_rays"] / (ms_per_step * 1e-3), clocks=clocks, launches=launches, rays_job=float(cnt["rays"]),
+               n_gpus=1, sharding="none", scaling="strong" if args.shard == "tiles" else "weak")
 
-    res = dict(ctx=ctx, bvh=bvh, cam=cam, w=w, h=h, spp=spp, bounces=bounces, tiles=tiles, cnt=cnt, ab=ab, mode_name=mode_name,
-               ms_per_step=ms_per_step, value=value, world=world, samples_per_s=samples_job / (ms_per_step * 1e-3), clocks=clocks,
-               launches=launches, rays_job=rays_job, stream=stream, torch=torch, dist=dist, modes=modes, variants=variants, order=order, barrier=barrier)
-    return res
-
-
-def run_e2e(args, res, rank, local, world):
-    """The same frame through the public API with host buffers.  N=1: `minipath_b200.render()` + wait() + image()
-    (mp_render: context, scene upload from host arrays, tile batches, RGBA8 tiles copied back under the image lock).
-    N>1: every rank uploads the host scene, renders its sample slice, one NCCL reduce, rank 0 resolves to host."""
-    import minipath_b200 as mp
-
-    torch, dist = res["torch"], res["dist"]
-    w, h, spp, bounces, bvh, cam = res["w"], res["h"], res["spp"], res["bounces"], res["bvh"], res["cam"]
-    raw = bvh.raw
-    scene_bytes = (raw.n_inner * (128 + 32) + raw.n_packets * (144 + 32 + 8 * 16) + raw.n_vertices * 32)
-    n_tiles = len(res["tiles"])
-    mode = res["modes"][res["mode_name"]]
-    if world == 1:
-        st = mp.RenderSettings(64, spp, (w, h), max_bounces=bounces, seed=7, mode=mode, order=res["order"], trace_kernel=res["variants"][res["mode_name"]])
+    if not args.no_e2e:
+        raw = bvh.raw
+        scene_bytes = raw.n_inner * (128 + 32) + raw.n_packets * (144 + 32 + 8 * 16) + raw.n_vertices * 32
+        st = mp.RenderSettings(64, spp, (w, h), max_bounces=bounces, seed=7, order=order,
+                               **({} if mode_name == auto_pipeline(bvh, bounces) else {"mode": modes[mode_name], "trace_kernel": variants[mode_name]}))
 
         def once():
             prog = mp.render(mp.Scene(bvh), cam, st, devices=[local])
             prog.wait()
             return prog.image()
-    else:
-        ctx, stream = res["ctx"], res["stream"]
-        film = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
-        host_img = np.empty((h, w, 4), np.uint8)
 
-        def once():
-            with torch.cuda.stream(stream):
-                ctx.upload_scene(bvh)
-                ctx.set_camera(cam.build_sampler((w, h)))
-                ctx.bind_film(film.data_ptr(), w, h)
-                film.zero_()
-                base = rank * spp
-                stp = mp.RenderSettings(64, spp, (w, h), max_bounces=bounces, seed=7, mode=mode, order=res["order"])
-                ctx.render_tiles(res["tiles"], stp.params(sample_base=base))
-                dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
-                if rank == 0:
-                    ctx.resolve_rgba8(spp * world, out=host_img)
-                stream.synchronize()
+        for _ in range(max(1, min(args.warmup, 2))):
+            once()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            once()
+        torch.cuda.synchronize()
+        secs = time.perf_counter() - t0
+        res["e2e"] = {"value": res["rays_job"] * args.steps / secs / 1e6, "unit": "Mrays/s", "ms_per_step": secs / args.steps * 1e3,
+                      "h2d_bytes_per_step": int(scene_bytes + len(tiles) * 16 + 52), "d2h_bytes_per_step": int(w * h * 4),
+                      "api": "minipath_b200.render()+wait()+image() [mp_render, MP_MODE_AUTO]: host scene arrays in, host RGBA8 image out"}
+    return res
+
+
+def measure_group(args, name, torch, dist, rank, local, world):
+    """N > 1 under torchrun: every rank joins ONE mp_group (NCCL communicator + shared-memory tile counter inside the library)."""
+    import minipath_b200 as mp
+
+    bvh, cam, w, h, spp, bounces = load_workload(name, args)
+    order = mp.ORDER_REFERENCE if args.order == "reference" else mp.ORDER_NEAR_FIRST
+    sampler = cam.build_sampler((w, h))
+    tiles = mp.full_screen_tiles(w, h, 64)
+    modes, variants = pipeline_tables(mp)
+    mode_name = auto_pipeline(bvh, bounces) if args.mode == "auto" else args.mode
+    shard = mp.SHARD_TILES if args.shard == "tiles" else mp.SHARD_SPP
+    spp_total = spp if args.shard == "tiles" else spp * world  # weak scaling: every GPU keeps the workload's spp
+
+    boot = [None, None]
+    if rank == 0:
+        boot = [mp.Group.unique_id(), f"/mp_b200_{os.getpid()}_{int(time.time() * 1e3) & 0xffffff}"]
+    dist.broadcast_object_list(boot, src=0)
+    g = mp.Group.for_rank(local, rank, world, boot[0], boot[1])
+    stream = torch.cuda.Stream()
+    ctx = g.context(0)
+    ctx.set_stream(stream.cuda_stream)
+    ctx.set_node_layout({"auto": mp.LAYOUT_AUTO, "decoded": mp.LAYOUT_DECODED, "quantised": mp.LAYOUT_QUANTISED}[args.layout])
+    g.set_trace_variant(variants[mode_name])
+    g.upload_scene(bvh)
+    g.set_camera(sampler)
+    g.create_film(w, h)
+    ctx.resolution = (w, h)
+    rgba = torch.empty((h, w), dtype=torch.int32, device="cuda")
+    timer = Timer(torch, stream)
+    st = mp.RenderSettings(64, spp_total, (w, h), max_bounces=bounces, seed=7, mode=modes[mode_name], order=order)
+
+    def step():
+        g.clear_film()
+        g.render(tiles, st.params(), shard=shard, min_batch=args.min_batch)
+        g.reduce_film()  # ncclReduce(sum) to rank 0 on the same stream
+        if rank == 0:
+            ctx.resolve_device(spp_total, rgba.data_ptr())
+
+    def barrier():
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def allsum(vals):
+        t = torch.tensor(vals, device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return [float(x) for x in t]
+
+    def allmax(vals):
+        t = torch.tensor(vals, device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(x) for x in t]
+
+    ctx.enable_counters(True)
+    ctx.reset_counters()
+    with torch.cuda.stream(stream):
+        step()
+    stream.synchronize()
+    cnt_local = ctx.counters()
+    ctx.enable_counters(False)
+    keys = ["rays", "camera_rays", "shadow_rays", "inner_visits", "packet_visits", "leaf_visits"]
+    cnt = dict(zip(keys, allsum([cnt_local[k] for k in keys])))
+
+    sampler_thread = ClockSampler(local) if rank == 0 else None
+    timer.run(step, args.warmup, 0)
+    ctx.reset_counters()
+    barrier()
+    if sampler_thread:
+        sampler_thread.start()
+    per_step = timer.run(step, 0, args.steps)
+    barrier()
+    clocks = sampler_thread.stop() if sampler_thread else None
+    launches = ctx.counters()["launches"]
+    total_ms = allmax([sum(per_step)])[0]
+    ms_per_step = total_ms / args.steps
+    stats = g.member_stats(0)
+    res = dict(name=name, ctx=ctx, group=g, bvh=bvh, cam=cam, w=w, h=h, spp=spp, bounces=bounces, tiles=tiles, cnt=cnt, ab={}, mode_name=mode_name,
+               ms_per_step=ms_per_step, per_step_ms=per_step, value=cnt["rays"] / (ms_per_step * 1e-3) / 1e6, world=world,
+               samples_per_s=cnt["camera_rays"] / (ms_per_step * 1e-3), clocks=clocks, launches=launches, rays_job=cnt["rays"],
+               n_gpus=world, sharding=args.shard, scaling="strong" if args.shard == "tiles" else "weak", spp_total=spp_total)
+
+    if args.timeline:  # where one step's time goes on every rank: device time of the render, of the reduce, tiles and batches taken
+        with torch.cuda.stream(stream):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            barrier()
+            g.clear_film()
+            ev[0].record(stream)
+            g.render(tiles, st.params(), shard=shard, min_batch=args.min_batch)
+            ev[1].record(stream)
+            g.reduce_film()
+            ev[2].record(stream)
+            if rank == 0:
+                ctx.resolve_device(spp_total, rgba.data_ptr())
+            ev[3].record(stream)
+            stream.synchronize()
+        s = g.member_stats(0)
+        mine = {"rank": rank, "render_ms": ev[0].elapsed_time(ev[1]), "reduce_wait_ms": ev[1].elapsed_time(ev[2]), "resolve_ms": ev[2].elapsed_time(ev[3]),
+                "tiles": s["tiles"], "batches": s["batches"]}
+        rows = [None] * world
+        dist.all_gather_object(rows, mine)
+        if rank == 0:
+            json.dump({"workload": name, "n_gpus": world, "sharding": args.shard, "min_batch": args.min_batch, "ranks": rows}, open(args.timeline, "w"), indent=1)
+
+    if not args.no_e2e:
+        raw = bvh.raw
+        scene_bytes = raw.n_inner * (128 + 32) + raw.n_packets * (144 + 32 + 8 * 16) + raw.n_vertices * 32
+        host_img = np.empty((h, w, 4), np.uint8)
+        phases = np.zeros(4)
+
+        def once(record=False):
+            t = [time.perf_counter()]
+            g.upload_scene(bvh)                       # host arrays -> every device
+            g.set_camera(cam.build_sampler((w, h)))
+            g.clear_film()
+            t.append(time.perf_counter())
+            g.render(tiles, st.params(), shard=shard, min_batch=args.min_batch)
+            t.append(time.perf_counter())
+            g.reduce_film()
+            g.resolve_rgba8(spp_total, host_img)       # rank 0: resolve + D2H into host memory; other ranks: drain their stream
+            t.append(time.perf_counter())
+            if record:
+                phases[:3] += np.diff(t)
             return host_img
 
-    for _ in range(max(1, min(args.warmup, 2))):
-        once()
-    res["barrier"]()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        once()
-    res["barrier"]()
-    secs = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([secs], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        secs = float(t[0])
-    return {"value": res["rays_job"] * args.steps / secs / 1e6, "unit": "Mrays/s", "ms_per_step": secs / args.steps * 1e3,
-            "h2d_bytes_per_step": int(scene_bytes + n_tiles * 16 + 52), "d2h_bytes_per_step": int(w * h * 4),
-            "api": "minipath_b200.render()+wait()+image() [mp_render]" if world == 1 else "Context upload_scene+render_tiles+NCCL reduce+resolve_rgba8"}
+        for _ in range(max(1, min(args.warmup, 2))):
+            once()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            once(record=True)
+        barrier()
+        secs = allmax([time.perf_counter() - t0])[0]
+        res["e2e"] = {"value": res["rays_job"] * args.steps / secs / 1e6, "unit": "Mrays/s", "ms_per_step": secs / args.steps * 1e3,
+                      "h2d_bytes_per_step": int(world * (scene_bytes + len(tiles) * 16 + 52)), "d2h_bytes_per_step": int(w * h * 4),
+                      "rank0_phase_ms": {"upload+camera+clear": phases[0] / args.steps * 1e3, "claim loop (launches)": phases[1] / args.steps * 1e3,
+                                         "reduce+resolve+D2H (waits for the render)": phases[2] / args.steps * 1e3},
+                      "api": "mp_group_* C ABI per rank: scene_upload + camera_set + film_create + render (shared tile counter) + reduce_film (NCCL) + resolve_rgba8"}
+    res["member_stats"] = stats
+    res["barrier"] = barrier
+    return res
 
 
-def roofline(args, res):
-    """Dominant kernel = the traversal (megakernel: the whole step is one launch; wavefront: wf_trace + wf_shadow).
-    Algorithmic work from the visit counters of the counted pass (reference visiting order), DESIGN.md §5."""
-    ctx, cnt = res["ctx"], res["cnt"]
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    hbm = float(peaks.get("hbm_gbs", 6650.0))
-    hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
-    fp32 = ctx.probe_fp32_tflops()
-    l2 = ctx.probe_l2_gbs(32 << 20)
+def roofline(args, res, probes):
+    """Whole step against the measured denominators.  Algorithmic work from the visit counters of the counted pass (reference
+    visiting order) with SURVEY §8(d)'s constants; `bound` = the roof that needs the longest time."""
+    cnt, n = res["cnt"], res["n_gpus"]
     secs = res["ms_per_step"] * 1e-3
-    bytes_ = cnt["inner_visits"] * BYTES_INNER + cnt["packet_visits"] * BYTES_PACKET + cnt["leaf_visits"] * BYTES_LEAF + cnt["rays"] * BYTES_RAY
-    flops = cnt["inner_visits"] * FLOPS_INNER + cnt["packet_visits"] * FLOPS_PACKET
+    ni, npk, nl, nr = cnt["inner_visits"], cnt["packet_visits"], cnt["leaf_visits"], cnt["rays"]
+    bytes_ = ni * (BYTES_INNER + BYTES_BOX) + npk * BYTES_PACKET + nl * BYTES_BOX + nr * BYTES_RAY
+    flops = ni * FLOPS_INNER + npk * FLOPS_PACKET
+    sectors = ni * 5 + npk * 6  # 32-byte sectors a lane gathers per visit: 152 -> 160-byte node record, 168 -> 192-byte packet record
     raw = res["bvh"].raw
-    scene_mb = (raw.n_inner * 160 + raw.n_packets * 176) / 1e6
-    t_fp32, t_l2, t_hbm = flops / (fp32 * 1e12), bytes_ / (l2 * 1e9), bytes_ / (hbm * 1e9)
-    # the BVH of every workload here is far smaller than the 126 MB L2, so the memory-side roof is L2, not HBM
-    mem_bound = ("hbm", t_hbm, hbm) if scene_mb > 100 else ("l2", t_l2, l2)
-    if t_fp32 >= mem_bound[1]:
-        out = {"bound": "fp32", "achieved": flops / secs / 1e12, "peak": fp32, "unit": "TFLOP/s", "frac": t_fp32 / secs}
+    scene_mb = (raw.n_inner * 160 + raw.n_packets * 192) / 1e6
+    fp32, l2, l1g, hbm = probes["fp32_tflops"], probes["l2_gbs"], probes["l1_gather_gsectors"], probes["hbm_gbs"]
+    times = {"fp32": flops / (fp32 * 1e12 * n), "l1_gather": sectors / (l1g * 1e9 * n),
+             ("hbm" if scene_mb > 100 else "l2"): bytes_ / ((hbm if scene_mb > 100 else l2) * 1e9 * n)}
+    bound = max(times, key=times.get)
+    if bound == "fp32":
+        out = {"bound": "fp32", "achieved": flops / secs / 1e12 / n, "peak": fp32, "unit": "TFLOP/s"}
+    elif bound == "l1_gather":
+        out = {"bound": "l1_gather", "achieved": sectors * 32 / secs / 1e9 / n, "peak": l1g * 32, "unit": "GB/s"}
     else:
-        out = {"bound": mem_bound[0], "achieved": bytes_ / secs / 1e9, "peak": mem_bound[2], "unit": "GB/s", "frac": mem_bound[1] / secs}
+        out = {"bound": bound, "achieved": bytes_ / secs / 1e9 / n, "peak": hbm if bound == "hbm" else l2, "unit": "GB/s"}
+    out["frac"] = times[bound] / secs
+    a_bytes = ni * ALT["BYTES_INNER"] + npk * ALT["BYTES_PACKET"] + nl * ALT["BYTES_LEAF"] + nr * ALT["BYTES_RAY"]
+    a_flops = ni * ALT["FLOPS_INNER"] + npk * ALT["FLOPS_PACKET"]
     traffic, traffic_note = None, "no ncu capture recorded for this workload/pipeline (scripts/ncu_traffic.py)"
     try:  # DRAM bytes of the traversal launches of one step, from an ncu capture of this very command line (profiles/traffic.json)
-        rec = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{args.workload}/{res['mode_name']}")
-        if rec and args.spp == 0 and args.bounces < 0 and res["world"] == 1:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{res['name']}/{res['mode_name']}")
+        if rec and res["world"] == 1:
             traffic = rec["dram_bytes_per_step"] * (res["spp"] / rec["spp"] if "spp" in rec else 1.0)  # captured at a reduced spp: linear in spp
             traffic_note = f"dram__bytes_read.sum + dram__bytes_write.sum over the {rec['launches']} traversal launches of one step ({rec['source']})"
-        elif rec:
-            traffic_note = "recorded for the workload's own spp/bounces on 1 GPU only"
     except Exception:
         pass
+    kernels = {"megakernel": "render_mega_kernel", "wavefront-octet": "wf_trace_octet_kernel+wf_shadow_octet_kernel",
+               "wavefront-thread": "wf_trace_kernel+wf_shadow_kernel", "wavefront-persist": "wf_trace_persist_kernel+wf_shadow_persist_kernel",
+               "wavefront-hybrid": "wf_primary_kernel + wf_trace_persist_kernel+wf_shadow_persist_kernel",
+               "wavefront-pool": "wf_trace_pool_kernel+wf_shadow_pool_kernel",
+               "wavefront-hybrid-pool": "wf_primary_kernel + wf_trace_pool_kernel+wf_shadow_pool_kernel",
+               "wavefront-hybrid-pool-s0": "wf_primary_kernel<SHADOW0> (camera rays + depth-0 sun rays) + wf_trace_pool_kernel + wf_shadow_pool_kernel"}
     out.update({
         "traffic": traffic, "traffic_note": traffic_note, "algorithmic_bytes_per_step": bytes_,
-        "kernel": {"megakernel": "render_mega_kernel", "wavefront-octet": "wf_trace_octet_kernel+wf_shadow_octet_kernel",
-                   "wavefront-thread": "wf_trace_kernel+wf_shadow_kernel",
-                   "wavefront-persist": "wf_trace_persist_kernel+wf_shadow_persist_kernel",
-                   "wavefront-hybrid": "wf_primary_kernel (camera rays: ray-gen + trace + shade) + wf_trace_persist_kernel+wf_shadow_persist_kernel",
-                   "wavefront-pool": "wf_trace_pool_kernel+wf_shadow_pool_kernel",
-                   "wavefront-hybrid-pool": "wf_primary_kernel (camera rays: ray-gen + trace + shade) + wf_trace_pool_kernel+wf_shadow_pool_kernel",
-                   "wavefront-hybrid-pool-s0": "wf_primary_kernel<SHADOW0> (camera rays + depth-0 sun rays: ray-gen + trace + shade + any-hit) + wf_trace_pool_kernel+wf_shadow_pool_kernel"}[res["mode_name"]] + " (share of step: see profiles/)",
-        "peak_source": "FP32 FMA and L2 read bandwidth measured by mp_probe_* in this run; HBM " + hbm_src,
-        "fp32": {"achieved_tflops": flops / secs / 1e12, "peak_tflops": fp32, "frac": t_fp32 / secs},
-        "l2": {"achieved_gbs": bytes_ / secs / 1e9, "peak_gbs": l2, "frac": t_l2 / secs},
-        "hbm": {"achieved_gbs": bytes_ / secs / 1e9, "peak_gbs": hbm, "frac": t_hbm / secs, "note": "BVH is cache-resident; HBM is not the roof"},
-        "per_ray": {"inner_visits": cnt["inner_visits"] / max(1, cnt["rays"]), "packet_visits": cnt["packet_visits"] / max(1, cnt["rays"]),
-                    "bytes": bytes_ / max(1, cnt["rays"]), "flops": flops / max(1, cnt["rays"])},
+        "constants": "SURVEY §8(d): bytes = 152 n_inner + 144 n_packet + 24 n_leaf + 52 rays; flops = 390 n_inner + 620 n_packet; sectors = 5 n_inner + 6 n_packet",
+        "scope": "whole step (ray-gen, shade and film included), all launches; per GPU at N>1",
+        "kernel": kernels[res["mode_name"]] + " (share of step: see profiles/)",
+        "peak_source": probes["source"],
+        "fp32": {"achieved_tflops": flops / secs / 1e12 / n, "peak_tflops": fp32, "frac": times["fp32"] / secs},
+        "l2": {"achieved_gbs": bytes_ / secs / 1e9 / n, "peak_gbs": l2, "frac": bytes_ / (l2 * 1e9 * n) / secs, "sweep": probes["l2_sweep"]},
+        "l1_gather": {"achieved_gsectors": sectors / secs / 1e9 / n, "peak_gsectors": l1g, "frac": times["l1_gather"] / secs,
+                      "note": "32-byte sectors per second an incoherent per-lane record gather gets from the L1 pipe (mp_probe_l1_gather)"},
+        "hbm": {"achieved_gbs": bytes_ / secs / 1e9 / n, "peak_gbs": hbm, "frac": bytes_ / (hbm * 1e9 * n) / secs,
+                "note": "roof only when the BVH outgrows the 126 MB L2 (soups); cache-resident here"},
+        "alt": {"constants": "round-1 device-record constants: bytes = 160 n_inner + 144 n_packet + 32 n_leaf + 52 rays; flops = 384 n_inner + 696 n_packet",
+                "l2_frac": a_bytes / (l2 * 1e9 * n) / secs, "fp32_frac": a_flops / (fp32 * 1e12 * n) / secs},
+        "per_ray": {"inner_visits": ni / max(1, nr), "packet_visits": npk / max(1, nr), "leaf_visits": nl / max(1, nr),
+                    "bytes": bytes_ / max(1, nr), "flops": flops / max(1, nr)},
         "scene_mb": scene_mb,
     })
     return out
 
 
+def run_probes(ctx, bvh):
+    """Roofline denominators measured on this device in this run."""
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    sweep, best = {}, 0.0
+    for mb in (8, 16, 32, 64, 96):          # all far below the 126 MB L2
+        for bps in (1, 2, 4):                # x 512 threads per SM
+            for vec in (16, 32):             # LDG.128 / LDG.256
+                v = ctx.probe_l2_gbs_shape(mb << 20, bps, vec)
+                sweep[f"{mb}MB/{bps * 512}thr/{vec}B"] = round(v, 1)
+                best = max(best, v)
+    raw = bvh.raw
+    n_rec = max(1024, int(raw.n_inner + raw.n_packets))
+    return {"fp32_tflops": ctx.probe_fp32_tflops(), "l2_gbs": best, "l2_sweep": sweep, "l1_gather_gsectors": ctx.probe_l1_gather(n_rec, 5),
+            "hbm_gbs": float(peaks.get("hbm_gbs", 6650.0)),
+            "source": "FP32 FMA rate, L2 read bandwidth (maximum of the sweep) and L1 gather rate measured by mp_probe_* in this run; HBM "
+                      + ("measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)")}
+
+
 def main():
     args = parse_args()
-    rank, local, world = init_dist(args)
-    if world > 1 and args.gpus != world:
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
         args.gpus = world
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
-    res = run_b200(args, rank, local, world)
-    e2e = None if args.no_e2e else run_e2e(args, res, rank, local, world)
+
+    import torch
+    import torch.distributed as dist
+
+    import minipath_b200 as mp
+
+    if not torch.cuda.is_available() or mp.device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device — the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        res = measure_group(args, args.workload, torch, dist, rank, local, world)
+    else:
+        res = measure_single(args, args.workload, torch, local)
+
     if rank == 0:
-        rl = roofline(args, res)
+        probes = run_probes(res["ctx"], res["bvh"])
+        rl = roofline(args, res, probes)
         cb = None
         if world == 1 and not args.no_cpu_baseline:
-            cb = cpu_baseline(args, res["bvh"], res["cam"], res["w"], res["h"], res["spp"], res["bounces"])
-        w, h, spp, bounces = res["w"], res["h"], res["spp"], res["bounces"]
+            cb = cpu_baseline(args, args.workload, res["bvh"], res["cam"], res["w"], res["h"], res["spp"], res["bounces"])
+        extra = None
+        if world == 1 and not args.no_extra and args.workload == DEFAULT_WORKLOAD:
+            r2 = measure_single(args, "teapot-1080p", torch, local, full=False)
+            rl2 = roofline(args, r2, probes)
+            extra = {"teapot-1080p": {"config": workload_config("teapot-1080p", args), "value": r2["value"], "unit": "Mrays/s", "ms_per_step": r2["ms_per_step"],
+                                      "pipeline": r2["mode_name"], "samples_per_s": r2["samples_per_s"], "e2e": r2.get("e2e"),
+                                      "roofline": {k: rl2[k] for k in ("bound", "achieved", "peak", "unit", "frac", "per_ray")},
+                                      "note": "BASELINE configs[1] (teapot 1920x1080, 64 spp, 5 bounces), same run, same timing rules"}}
+            r2["ctx"].close()
         st = res["bvh"].stats()
         line = {
             "metric": "Mrays/s", "value": res["value"], "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak" if args.shard == "spp" else "strong",
-            "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic camera samples (counter-based RNG) on " + ("the reference's data/%s.obj" % WORKLOADS[args.workload][0]
-                                                                         if WORKLOADS[args.workload][0] != "atrium" else
-                                                                         "a procedural Sponza STAND-IN (sponza.obj is absent from the reference)"),
-            "samples_per_s": res["samples_per_s"],
-            "config": {"workload": args.workload, "resolution": [w, h], "spp_per_gpu": spp, "spp_total": spp * world if args.shard == "spp" else spp,
-                       "max_bounces": bounces, "tile_size": 64, "pipeline": res["mode_name"], "traversal_order": args.order, "node_layout": args.layout,
-                       "pipeline_ab_ms": res["ab"], "sharding": args.shard if world > 1 else "none",
-                       "bvh": {"triangles": st["n_triangles"], "inner_nodes": st["n_inner"], "packets": st["n_packets"]},
-                       "l2": "flushed between timed steps (256 MB fill outside the event pairs)",
-                       "note": "max_bounces>0 is the extension integrator (the reference traces primary rays only)"},
+            "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": res["scaling"],
+            "vs_baseline": None, "dtype": "f32", "data": data_note(args.workload), "samples_per_s": res["samples_per_s"],
+            "config": workload_config(args.workload, args),
+            "pipeline": {"picked": res["mode_name"], "how": "MP_MODE_AUTO (what render() runs)" if args.mode == "auto" else "forced by --mode",
+                         "traversal_order": args.order, "node_layout": args.layout, "pipeline_ab_ms": res["ab"],
+                         "sharding": res["sharding"], "spp_total": res.get("spp_total", res["spp"]),
+                         "bvh": {"triangles": st["n_triangles"], "inner_nodes": st["n_inner"], "packets": st["n_packets"]},
+                         "per_step_ms_rank0": res["per_step_ms"], "member_stats_rank0": res.get("member_stats")},
             "rays_per_step": res["rays_job"], "gpu_launches": int(res["launches"]), "clocks": res["clocks"],
-            "roofline": rl, "cpu_baseline": cb, "e2e": e2e,
+            "roofline": rl, "cpu_baseline": cb, "e2e": res.get("e2e"), "extra": extra,
         }
         print(json.dumps(line), flush=True)
-    res["ctx"].close()
     if world > 1:
-        res["dist"].barrier()
-        res["dist"].destroy_process_group()
+        res["barrier"]()
+        res["group"].close()
+        dist.barrier()
+        dist.destroy_process_group()
+    else:
+        res["ctx"].close()
 
 
 if __name__ == "__main__":

@@ -214,6 +214,8 @@ int mp_ctx_pool_clear(void);
 /* Run on a caller-owned CUDA stream (cudaStream_t as void*); NULL → the context's own stream. */
 int mp_ctx_set_stream(MpCtx* ctx, void* cuda_stream);
 int mp_ctx_sync(MpCtx* ctx);
+/* The stream the context launches on (cudaStream_t as void*): what a caller hands to its own collectives or copies. */
+int mp_ctx_stream(MpCtx* ctx, void** out_cuda_stream);
 /* Which traversal kernel serves mp_trace_rays* and the wavefront pipeline (same visiting order, same bits):
  * THREAD = one thread per ray, SoA node rows, local-memory stack (trace.cuh; default);
  * OCTET  = eight lanes per ray, child-major 16-byte records, shared-memory stack, self-refilling octets (octet.cuh). */
@@ -256,6 +258,12 @@ int mp_last_device_ms(MpCtx* ctx, float* out_ms);
  * FP32 FMA throughput (TFLOP/s, 2 flop per FMA) and L2 read bandwidth (GB/s) over a buffer of `bytes`. */
 int mp_probe_fp32_tflops(MpCtx* ctx, float* out_tflops);
 int mp_probe_l2_gbs(MpCtx* ctx, size_t bytes, float* out_gbs);
+/* One shape of the L2 probe (1..4 blocks of 512 threads per SM, 16- or 32-byte loads): the caller sweeps shapes and buffer sizes
+ * and takes the maximum as the L2 roof. */
+int mp_probe_l2_gbs_shape(MpCtx* ctx, size_t bytes, uint32_t blocks_per_sm, uint32_t vec_bytes, float* out_gbs);
+/* L1 gather roof of an incoherent traversal: every lane fetches its own 5- or 6-sector record (160 / 192 bytes) with 256-bit
+ * loads; result in 10^9 32-byte sectors per second over the whole GPU. */
+int mp_probe_l1_gather(MpCtx* ctx, uint32_t n_records, uint32_t sectors_per_record, float* out_gsectors_per_s);
 
 /* Scene<TriangleBvh> → device (borrowed host arrays are copied; caller keeps ownership). */
 int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* bvh);
@@ -353,7 +361,47 @@ typedef struct MpTileQueue MpTileQueue;
 int mp_tileq_open(const char* name, int create, MpTileQueue** out);
 int mp_tileq_reset(MpTileQueue* q);
 int mp_tileq_next(MpTileQueue* q, uint64_t batch, uint64_t* out_first); /* fetch_add(batch) */
+int mp_tileq_peek(MpTileQueue* q, uint64_t* out_next);                   /* load() */
+/* Barrier over the `world` processes that share the segment (used to rewind the counter between renders); timeout_ms = 0 waits forever. */
+int mp_tileq_barrier(MpTileQueue* q, uint32_t world, uint32_t timeout_ms);
 int mp_tileq_close(MpTileQueue* q, int unlink);
+
+/* ---- multi-GPU groups: render()'s scheduler over the GPUs of one box (machinery.rs:51-116,205-209) ----
+ * Workers = GPUs.  MP_SHARD_TILES: the devices pull batches of consecutive tiles of the tile list from ONE shared counter
+ * (remaining / (2 * devices) tiles at a time, at least min_batch: coarse while work is plentiful, fine at the tail) — total work
+ * fixed, "strong" scaling (BASELINE configs[2]).  MP_SHARD_SPP: every device renders all tiles with its own contiguous slice of
+ * the sample indices (BASELINE configs[3]).  Either way each device accumulates into its own zero-initialised full-resolution
+ * film and ONE ncclReduce(sum, f32 x 4 per pixel) over NVLink combines them on rank 0, which resolves.  No traffic between GPUs
+ * during traversal.  NCCL is dlopen()ed when the first group with more than one device is made. */
+typedef struct MpGroup MpGroup;
+#define MP_SHARD_TILES 0u
+#define MP_SHARD_SPP 1u
+#define MP_NCCL_ID_BYTES 128
+/* One process, n devices (NULL / 0: all): a host thread per device during mp_group_render, ncclCommInitAll. */
+int mp_group_create(const int* devices, int n_devices, MpGroup** out);
+/* One process per GPU (e.g. torchrun): rank 0 makes the NCCL id and the caller ships its 128 bytes to the other ranks; the tile
+ * counter lives in POSIX shared memory under queue_name (created by rank 0, which must therefore come first: create it before
+ * the id is shipped). */
+int mp_group_unique_id(uint8_t out[MP_NCCL_ID_BYTES]);
+int mp_group_create_rank(int device, int rank, int world, const uint8_t id[MP_NCCL_ID_BYTES], const char* queue_name, MpGroup** out);
+int mp_group_destroy(MpGroup* g);
+int mp_group_size(MpGroup* g, int* out_local, int* out_world);
+int mp_group_ctx(MpGroup* g, int local_index, MpCtx** out);  /* borrowed: counters, variants, streams of one member */
+int mp_group_scene_upload(MpGroup* g, const MpFlatBvh* bvh);   /* replicated on every device */
+int mp_group_camera_set(MpGroup* g, const MpCameraSampler* sampler);
+int mp_group_set_trace_variant(MpGroup* g, uint32_t variant);
+int mp_group_film_create(MpGroup* g, uint32_t width, uint32_t height); /* zeroed films; same size again = clear */
+/* Launches this process's share of the frame and returns when its claim loops have ended (the last batches may still be running
+ * on the devices; everything later is stream-ordered behind them). */
+int mp_group_render(MpGroup* g, const MpTile* tiles, uint32_t n_tiles, const MpRenderParams* params, uint32_t shard, uint32_t min_batch);
+int mp_group_reduce_film(MpGroup* g);                                  /* ncclReduce(sum) to rank 0, in place, asynchronous */
+int mp_group_resolve_rgba8(MpGroup* g, uint32_t spp_total, uint8_t* host_out); /* rank 0: resolve + D2H; other ranks: drain */
+int mp_group_read_film(MpGroup* g, int local_index, float* host_out);
+int mp_group_sync(MpGroup* g);
+/* Device time (CUDA events) from the start of the last mp_group_render to the end of its last batch — or of the reduce, if one
+ * followed — maximum over this process's devices. */
+int mp_group_last_ms(MpGroup* g, float* out_ms);
+int mp_group_member_stats(MpGroup* g, int local_index, uint64_t* out_batches, uint64_t* out_tiles, float* out_ms);
 
 #ifdef __cplusplus
 }

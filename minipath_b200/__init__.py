@@ -21,6 +21,8 @@ from ._ffi import (  # noqa: F401  (re-exported)
     NO_HIT,
     ORDER_NEAR_FIRST,
     ORDER_REFERENCE,
+    SHARD_SPP,
+    SHARD_TILES,
     TRACE_HYBRID,
     TRACE_HYBRID_POOL,
     TRACE_HYBRID_POOL_S0,
@@ -429,15 +431,25 @@ def _tiles_arg(tiles):
 
 
 class Context:
-    def __init__(self, device=0):
+    def __init__(self, device=0, _borrowed=None):
         self._h = C.c_void_p()
-        check(lib.mp_ctx_create(device, C.byref(self._h)))
+        self._owned = _borrowed is None
+        if _borrowed is None:
+            check(lib.mp_ctx_create(device, C.byref(self._h)))
+        else:
+            self._h = _borrowed  # a group member's context: the group owns it
         self.resolution = None
 
     def close(self):
         if getattr(self, "_h", None):
-            lib.mp_ctx_destroy(self._h)
+            if self._owned:
+                lib.mp_ctx_destroy(self._h)
             self._h = None
+
+    def stream(self):
+        out = C.c_void_p()
+        check(lib.mp_ctx_stream(self._h, C.byref(out)))
+        return out.value
 
     __del__ = close
 
@@ -478,6 +490,17 @@ class Context:
     def probe_l2_gbs(self, nbytes=32 << 20):
         out = C.c_float()
         check(lib.mp_probe_l2_gbs(self._h, nbytes, C.byref(out)))
+        return out.value
+
+    def probe_l2_gbs_shape(self, nbytes, blocks_per_sm, vec_bytes):
+        out = C.c_float()
+        check(lib.mp_probe_l2_gbs_shape(self._h, nbytes, blocks_per_sm, vec_bytes, C.byref(out)))
+        return out.value
+
+    def probe_l1_gather(self, n_records, sectors_per_record=5):
+        """10^9 32-byte sectors per second the L1 pipe delivers to an incoherent per-lane gather of records."""
+        out = C.c_float()
+        check(lib.mp_probe_l1_gather(self._h, n_records, sectors_per_record, C.byref(out)))
         return out.value
 
     def upload_scene(self, bvh):
@@ -542,6 +565,102 @@ class Context:
         return rays
 
 
+class Group:
+    """The GPUs of one box as the workers of render()'s tile scheduler (machinery.rs:51-116,205-209) — mp_group_*.
+
+    ``Group(devices=[0, 1, ...])``: one process, a host thread per device while a frame renders.
+    ``Group.for_rank(device, rank, world, nccl_id, queue_name)``: one process per GPU (torchrun); rank 0 makes ``nccl_id`` with
+    ``Group.unique_id()`` and the caller ships it.  The films are combined by one NCCL sum-reduce to rank 0."""
+
+    def __init__(self, devices=None, _handle=None):
+        self._h = C.c_void_p()
+        if _handle is not None:
+            self._h = _handle
+        else:
+            arr, n = (None, 0) if not devices else ((C.c_int * len(devices))(*devices), len(devices))
+            check(lib.mp_group_create(arr, n, C.byref(self._h)))
+        self.resolution = None
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_uint8 * _ffi.NCCL_ID_BYTES)()
+        check(lib.mp_group_unique_id(buf))
+        return bytes(buf)
+
+    @classmethod
+    def for_rank(cls, device, rank, world, nccl_id=None, queue_name=None):
+        h = C.c_void_p()
+        idbuf = None if nccl_id is None else (C.c_uint8 * _ffi.NCCL_ID_BYTES).from_buffer_copy(nccl_id)
+        check(lib.mp_group_create_rank(device, rank, world, idbuf, None if queue_name is None else queue_name.encode(), C.byref(h)))
+        return cls(_handle=h)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.mp_group_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def size(self):
+        a, b = C.c_int(), C.c_int()
+        check(lib.mp_group_size(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def context(self, local_index=0):
+        h = C.c_void_p()
+        check(lib.mp_group_ctx(self._h, local_index, C.byref(h)))
+        ctx = Context(_borrowed=h)
+        ctx.resolution = self.resolution
+        return ctx
+
+    def upload_scene(self, bvh):
+        check(lib.mp_group_scene_upload(self._h, bvh._ptr))
+
+    def set_camera(self, sampler):
+        check(lib.mp_group_camera_set(self._h, C.byref(sampler)))
+
+    def set_trace_variant(self, variant):
+        check(lib.mp_group_set_trace_variant(self._h, variant))
+
+    def create_film(self, width, height):
+        check(lib.mp_group_film_create(self._h, width, height))
+        self.resolution = (width, height)
+
+    clear_film = lambda self: self.create_film(*self.resolution)  # noqa: E731  (same size again = clear)
+
+    def render(self, tiles, params, shard=SHARD_TILES, min_batch=0):
+        arr, ptr, n = _tiles_arg(tiles)
+        check(lib.mp_group_render(self._h, ptr, n, C.byref(params), shard, min_batch))
+
+    def reduce_film(self):
+        check(lib.mp_group_reduce_film(self._h))
+
+    def resolve_rgba8(self, spp_total, out=None):
+        w, h = self.resolution
+        img = np.empty((h, w, 4), np.uint8) if out is None else out
+        check(lib.mp_group_resolve_rgba8(self._h, spp_total, img.ctypes.data))
+        return img
+
+    def read_film(self, local_index=0):
+        w, h = self.resolution
+        film = np.empty((h, w, 4), np.float32)
+        check(lib.mp_group_read_film(self._h, local_index, film.ctypes.data))
+        return film
+
+    def sync(self):
+        check(lib.mp_group_sync(self._h))
+
+    def last_ms(self):
+        ms = C.c_float()
+        check(lib.mp_group_last_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def member_stats(self, local_index=0):
+        b, t, ms = C.c_uint64(), C.c_uint64(), C.c_float()
+        check(lib.mp_group_member_stats(self._h, local_index, C.byref(b), C.byref(t), C.byref(ms)))
+        return {"batches": b.value, "tiles": t.value, "ms": ms.value}
+
+
 class TileQueue:
     """Cross-process tile counter in shared memory (the AtomicUsize of machinery.rs:43,205-209)."""
 
@@ -557,6 +676,14 @@ class TileQueue:
         out = C.c_uint64()
         check(lib.mp_tileq_next(self._h, batch, C.byref(out)))
         return out.value
+
+    def peek(self):
+        out = C.c_uint64()
+        check(lib.mp_tileq_peek(self._h, C.byref(out)))
+        return out.value
+
+    def barrier(self, world, timeout_ms=60000):
+        check(lib.mp_tileq_barrier(self._h, world, timeout_ms))
 
     def close(self):
         if getattr(self, "_h", None):

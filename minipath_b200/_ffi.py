@@ -21,6 +21,8 @@ ORDER_REFERENCE, ORDER_NEAR_FIRST = 0, 1
 MODE_AUTO = 2
 TRACE_THREAD, TRACE_OCTET, TRACE_PERSIST, TRACE_HYBRID, TRACE_POOL, TRACE_HYBRID_POOL, TRACE_HYBRID_POOL_S0 = 0, 1, 2, 3, 4, 5, 6
 LAYOUT_QUANTISED, LAYOUT_DECODED, LAYOUT_AUTO = 0, 1, 2
+SHARD_TILES, SHARD_SPP = 0, 1
+NCCL_ID_BYTES = 128
 
 
 class MpError(RuntimeError):
@@ -200,12 +202,15 @@ PROTOTYPES = {
     "mp_ctx_set_trace_variant": (_i, [_vp, _u32]),
     "mp_ctx_set_node_layout": (_i, [_vp, _u32]),
     "mp_ctx_sync": (_i, [_vp]),
+    "mp_ctx_stream": (_i, [_vp, _P(_vp)]),
     "mp_ctx_enable_counters": (_i, [_vp, _i]),
     "mp_counters": (_i, [_vp, _P(MpCounters)]),
     "mp_counters_reset": (_i, [_vp]),
     "mp_last_device_ms": (_i, [_vp, _P(C.c_float)]),
     "mp_probe_fp32_tflops": (_i, [_vp, _P(C.c_float)]),
     "mp_probe_l2_gbs": (_i, [_vp, C.c_size_t, _P(C.c_float)]),
+    "mp_probe_l2_gbs_shape": (_i, [_vp, C.c_size_t, _u32, _u32, _P(C.c_float)]),
+    "mp_probe_l1_gather": (_i, [_vp, _u32, _u32, _P(C.c_float)]),
     "mp_scene_upload": (_i, [_vp, _P(MpFlatBvh)]),
     "mp_camera_set": (_i, [_vp, _P(MpCameraSampler)]),
     "mp_film_create": (_i, [_vp, _u32, _u32]),
@@ -240,7 +245,26 @@ PROTOTYPES = {
     "mp_tileq_open": (_i, [C.c_char_p, _i, _P(_vp)]),
     "mp_tileq_reset": (_i, [_vp]),
     "mp_tileq_next": (_i, [_vp, _u64, _P(_u64)]),
+    "mp_tileq_peek": (_i, [_vp, _P(_u64)]),
+    "mp_tileq_barrier": (_i, [_vp, _u32, _u32]),
     "mp_tileq_close": (_i, [_vp, _i]),
+    "mp_group_create": (_i, [_P(_i), _i, _P(_vp)]),
+    "mp_group_unique_id": (_i, [_vp]),
+    "mp_group_create_rank": (_i, [_i, _i, _i, _vp, C.c_char_p, _P(_vp)]),
+    "mp_group_destroy": (_i, [_vp]),
+    "mp_group_size": (_i, [_vp, _P(_i), _P(_i)]),
+    "mp_group_ctx": (_i, [_vp, _i, _P(_vp)]),
+    "mp_group_scene_upload": (_i, [_vp, _P(MpFlatBvh)]),
+    "mp_group_camera_set": (_i, [_vp, _P(MpCameraSampler)]),
+    "mp_group_set_trace_variant": (_i, [_vp, _u32]),
+    "mp_group_film_create": (_i, [_vp, _u32, _u32]),
+    "mp_group_render": (_i, [_vp, _P(MpTile), _u32, _P(MpRenderParams), _u32, _u32]),
+    "mp_group_reduce_film": (_i, [_vp]),
+    "mp_group_resolve_rgba8": (_i, [_vp, _u32, _vp]),
+    "mp_group_read_film": (_i, [_vp, _i, _vp]),
+    "mp_group_sync": (_i, [_vp]),
+    "mp_group_last_ms": (_i, [_vp, _P(C.c_float)]),
+    "mp_group_member_stats": (_i, [_vp, _i, _P(_u64), _P(_u64), _P(C.c_float)]),
 }
 
 

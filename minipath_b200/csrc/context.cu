@@ -271,6 +271,12 @@ int mp_ctx_sync(MpCtx* ctx) {
     return MP_OK;
 }
 
+int mp_ctx_stream(MpCtx* ctx, void** out) {
+    if (!ctx || !out) return fail(MP_EINVAL, "null argument");
+    *out = (void*)ctx->stream;
+    return MP_OK;
+}
+
 int mp_ctx_enable_counters(MpCtx* ctx, int on) {
     if (!ctx) return fail(MP_EINVAL, "null context");
     ctx->count_visits = on != 0;
@@ -389,6 +395,7 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaGetLastError());
     ctx->decoded_ok = h_flags == 0;  // a child box with min > max: stay on the quantised records
+    ctx->scene.minmax_ok = h_flags == 0 ? 1u : 0u;
     ctx->decoded_small = s_inner_w + s_pack_w <= (1u << 20);
     ctx->max_stack = st.max_stack;
     ctx->has_scene = true;

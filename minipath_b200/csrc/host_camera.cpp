@@ -7,8 +7,10 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstring>
 #include <random>
+#include <thread>
 #include <vector>
 
 #include "host_common.h"
@@ -133,7 +135,9 @@ int mp_tile_ordering(uint32_t min_x, uint32_t min_y, uint32_t max_x, uint32_t ma
 // exactly like workers do on RenderState::next_tile_index (machinery.rs:205-209).
 // ---------------------------------------------------------------------------------------------------
 struct MpTileQueue {
-    std::atomic<uint64_t>* counter;
+    std::atomic<uint64_t>* counter;     // byte 0 of the 64-byte segment: next_tile_index
+    std::atomic<uint32_t>* arrived;     // byte 8: ranks waiting at the barrier
+    std::atomic<uint32_t>* generation;  // byte 12: barrier generation (sense reversal)
     char name[200];
 };
 
@@ -151,8 +155,14 @@ int mp_tileq_open(const char* name, int create, MpTileQueue** out) {
     if (p == MAP_FAILED) return fail(MP_EIO, "mmap(%s) failed: %s", name, strerror(errno));
     MpTileQueue* q = new MpTileQueue();
     q->counter = reinterpret_cast<std::atomic<uint64_t>*>(p);
+    q->arrived = reinterpret_cast<std::atomic<uint32_t>*>((char*)p + 8);
+    q->generation = reinterpret_cast<std::atomic<uint32_t>*>((char*)p + 12);
     snprintf(q->name, sizeof q->name, "%s", name);
-    if (create) q->counter->store(0, std::memory_order_release);
+    if (create) {
+        q->counter->store(0, std::memory_order_release);
+        q->arrived->store(0, std::memory_order_release);
+        q->generation->store(0, std::memory_order_release);
+    }
     *out = q;
     return MP_OK;
 }
@@ -164,6 +174,32 @@ int mp_tileq_reset(MpTileQueue* q) {
 int mp_tileq_next(MpTileQueue* q, uint64_t batch, uint64_t* out_first) {
     if (!q || !out_first) return fail(MP_EINVAL, "null argument");
     *out_first = q->counter->fetch_add(batch, std::memory_order_acq_rel);
+    return MP_OK;
+}
+int mp_tileq_peek(MpTileQueue* q, uint64_t* out_next) {
+    if (!q || !out_next) return fail(MP_EINVAL, "null argument");
+    *out_next = q->counter->load(std::memory_order_acquire);
+    return MP_OK;
+}
+// Sense-reversing barrier over the ranks that share the segment: the last arrival bumps the generation, the others spin on it
+// (yielding; a render step lasts milliseconds to seconds, a barrier microseconds).  timeout_ms bounds the wait for a rank that died.
+int mp_tileq_barrier(MpTileQueue* q, uint32_t world, uint32_t timeout_ms) {
+    if (!q || world == 0) return fail(MP_EINVAL, "bad argument");
+    if (world == 1) return MP_OK;
+    const uint32_t gen = q->generation->load(std::memory_order_acquire);
+    if (q->arrived->fetch_add(1, std::memory_order_acq_rel) + 1 == world) {
+        q->arrived->store(0, std::memory_order_release);
+        q->generation->store(gen + 1, std::memory_order_release);
+        return MP_OK;
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    for (uint32_t spins = 0; q->generation->load(std::memory_order_acquire) == gen; ++spins) {
+        if ((spins & 63u) == 63u) {
+            std::this_thread::yield();
+            if (timeout_ms && std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(timeout_ms))
+                return fail(MP_ESTATE, "tile-queue barrier timed out after %u ms (%s): a rank is missing", timeout_ms, q->name);
+        }
+    }
     return MP_OK;
 }
 int mp_tileq_close(MpTileQueue* q, int unlink_it) {

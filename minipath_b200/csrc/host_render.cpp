@@ -64,7 +64,10 @@ struct MpRenderProgress {
     std::chrono::steady_clock::duration end_elapsed{};
     // RenderProgress (machinery.rs:125-129)
     size_t worker_count = 0;
-    size_t batch = 1;
+    size_t batch = 0;      // fixed tiles per batch (settings.tiles_per_batch), 0 = sized by the library per claim
+    size_t min_batch = 4;  // library-sized batches: never below this many tiles
+    std::atomic<size_t> tiles_done{0};  // tiles whose pixels are in `image`
+    std::mutex join_mutex;              // wait() / free() may be called from several threads (RenderProgress is Sync)
     uint32_t trace_variant = MP_TRACE_THREAD;
     std::vector<std::thread> threads;
     std::atomic<size_t> threads_finished{0};
@@ -109,10 +112,11 @@ static int finish_batch(MpRenderProgress* p, MpCtx* ctx, Pending& b, int slot) {
                 memcpy(&p->image[((size_t)y * s.resolution_x + t.min_x) * 4], &buffer[((i * s.tile_size + (y - t.min_y)) * s.tile_size) * 4], w * 4);
         }
     }
+    // the reference estimates `finished` as next_tile_index - worker_count (machinery.rs:96); batches make that estimate too coarse,
+    // so the tiles that have reached the image are counted exactly
+    const size_t done = p->tiles_done.fetch_add(b.n, std::memory_order_acq_rel) + b.n;
     if (p->finished) {
-        const size_t in_flight = p->worker_count * p->batch;
-        const size_t next_id = std::min(p->next_tile_index.load(std::memory_order_acquire), total + in_flight);
-        MpProgressSnapshot snap{next_id > in_flight ? std::min(next_id - in_flight, total) : 0, total};  // saturating_sub (machinery.rs:96)
+        MpProgressSnapshot snap{std::min(done, total), total};
         for (size_t i = 0; i < b.n; ++i) p->finished(p->user, tiles[i], snap);
     }
     return MP_OK;
@@ -153,20 +157,31 @@ static void worker_main(MpRenderProgress* p, int device) {
     Pending pending[2];
     int slot = 0;
     while (!rc) {
-        const size_t first = p->next_tile_index.fetch_add(p->batch, std::memory_order_acq_rel);  // get_next_tile
+        // get_next_tile (machinery.rs:205-209), a batch at a time.  Library-sized batches: half of an equal share of what is left
+        // (guided self-scheduling: coarse while work is plentiful so that every wavefront pass stays wide, fine at the tail so that
+        // the devices finish together), never below min_batch, which for one device is "enough tiles for one full-width pass".
+        size_t want = p->batch;
+        if (want == 0) {
+            const size_t cur = p->next_tile_index.load(std::memory_order_acquire);
+            if (cur >= total) break;
+            want = p->worker_count == 1 ? p->min_batch : std::max(p->min_batch, std::min<size_t>(64, (total - cur) / (2 * p->worker_count)));
+        }
+        const size_t first = p->next_tile_index.fetch_add(want, std::memory_order_acq_rel);
         if (first >= total) break;
-        const size_t n = std::min(p->batch, total - first);
+        const size_t n = std::min(want, total - first);
         if (p->started)
             for (size_t i = 0; i < n; ++i) p->started(p->user, p->tile_ordering[first + i]);
         if (first == 0 && n == total) {
             // the whole frame in one batch (default for one device): resolve straight into the pinned image, no tile staging
             rc = mp_render_tile_range(ctx, 0, (uint32_t)n, &params);
             lap("launch");
+            if (!rc) rc = mp_ctx_sync(ctx);  // wait for the render OUTSIDE the image lock: image() stays responsive meanwhile
             if (!rc) {
                 std::lock_guard<std::mutex> g(p->image_mutex);
                 rc = mp_film_resolve_rgba8(ctx, s.sample_count, p->image);
             }
             lap("render+resolve");
+            p->tiles_done.fetch_add(n, std::memory_order_acq_rel);
             if (!rc && p->finished) {
                 const MpProgressSnapshot snap{total, total};
                 for (size_t i = 0; i < n; ++i) p->finished(p->user, p->tile_ordering[i], snap);
@@ -264,11 +279,17 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
         if (settings->trace_kernel) p->trace_variant = settings->trace_kernel - 1;
     }
     p->worker_count = devs.size();
-    // default batch: one device takes the frame in one batch (every sample pass then runs at full width; small batches
-    // leave the late, thin bounce queues launch-bound); several devices take a quarter of their share at a time so the
-    // shared counter still balances the tail.  Callers that want tile callbacks to trickle in set tiles_per_batch.
-    p->batch = settings->tiles_per_batch ? settings->tiles_per_batch
-                                         : (devs.size() == 1 ? std::max<size_t>(1, n_tiles) : std::max<size_t>(32, n_tiles / (4 * devs.size())));
+    // Batches (tiles claimed per fetch_add).  tiles_per_batch set: exactly that.  Otherwise the library sizes them: a wavefront pass
+    // carries about 32 M paths whatever the batch (context_render.inc: WF_TARGET_PATHS), so a batch of 32 M / (tile pixels * spp)
+    // tiles is one full-width pass — batches of at least that size cost nothing and keep abort(), progress() and the tile
+    // callbacks at pass granularity (a 4K 1024-spp frame is hundreds of batches, not one).  The megakernel (one launch per batch)
+    // gets the same bound: the reference bench's 2048x1536x10 spp frame stays a single launch.
+    {
+        const size_t paths_per_tile = (size_t)settings->tile_size * settings->tile_size * settings->sample_count;
+        const size_t pass_tiles = ((size_t)1 << 25) / std::max<size_t>(1, paths_per_tile);
+        p->min_batch = devs.size() == 1 ? std::max<size_t>(4, pass_tiles) : 4;
+        p->batch = settings->tiles_per_batch;
+    }
     p->started = started, p->finished = finished, p->user = user;
     p->start_time = std::chrono::steady_clock::now();
     try {
@@ -285,9 +306,8 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
 
 int mp_progress_snapshot(MpRenderProgress* p, MpProgressSnapshot* out) {  // machinery.rs:133-142
     if (!p || !out) return fail(MP_EINVAL, "null argument");
-    const size_t total = p->tile_ordering.size(), in_flight = p->worker_count * p->batch;
-    const size_t next_id = p->next_tile_index.load(std::memory_order_acquire);
-    out->finished = next_id > in_flight ? std::min(next_id - in_flight, total) : 0;
+    const size_t total = p->tile_ordering.size();
+    out->finished = std::min(p->tiles_done.load(std::memory_order_acquire), total);
     out->total = total;
     return MP_OK;
 }
@@ -310,9 +330,12 @@ int mp_progress_abort(MpRenderProgress* p) {  // machinery.rs:161-165
 }
 int mp_progress_wait(MpRenderProgress* p) {  // machinery.rs:169-173
     if (!p) return fail(MP_EINVAL, "null argument");
-    for (auto& t : p->threads)
-        if (t.joinable()) t.join();
-    p->threads.clear();
+    {
+        std::lock_guard<std::mutex> j(p->join_mutex);
+        for (auto& t : p->threads)
+            if (t.joinable()) t.join();
+        p->threads.clear();
+    }
     std::lock_guard<std::mutex> g(p->error_mutex);
     if (p->error_code != MP_OK) return fail(p->error_code, "render worker failed: %s", p->error.c_str());
     return MP_OK;
@@ -333,8 +356,12 @@ int mp_progress_image_ptr(MpRenderProgress* p, const uint8_t** out, size_t* out_
 int mp_progress_free(MpRenderProgress* p) {
     if (!p) return MP_OK;
     mp_progress_abort(p);
-    for (auto& t : p->threads)
-        if (t.joinable()) t.join();
+    {
+        std::lock_guard<std::mutex> j(p->join_mutex);
+        for (auto& t : p->threads)
+            if (t.joinable()) t.join();
+        p->threads.clear();
+    }
     delete p;
     return MP_OK;
 }

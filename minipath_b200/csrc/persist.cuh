@@ -40,7 +40,7 @@ __device__ __forceinline__ void persist_run(const Scene& sc, uint32_t n, uint32_
                 if (next >= n) break;
                 cur = next, next += stride;
                 fetch(cur, r);
-                nanpath = ray_needs_nanpath(r);
+                nanpath = ray_needs_nanpath(sc, r);
                 if (LAYOUT == MP_LAYOUT_DECODED) sel = ray_sel(r);
                 best = Hit{MPD_FLT_MAX, 0.0f, 0.0f, MP_NO_HIT};
                 stk[0] = make_uint2(sc.root, __float_as_uint(MPD_NINF));

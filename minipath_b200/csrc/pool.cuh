@@ -43,6 +43,15 @@ namespace mpd {
                                    // beat 5 (96): default workload 32.0 -> 30.0 ms, while the stand-in (QUANTISED records) loses 10 % with 4
 #endif
 #define POOL_BLOCKS_FOR(LAYOUT) ((LAYOUT) == MP_LAYOUT_DECODED ? POOL_MIN_BLOCKS_DECODED : POOL_MIN_BLOCKS)
+#ifndef POOL_MIXED
+#define POOL_MIXED 0    // 1: the QUANTISED instantiations read DECODED inner nodes (7 x LDG.256) and keep the quantised packets
+#endif
+#ifndef POOL_PUSH_RANK
+#define POOL_PUSH_RANK 1 // hit children go to the stack as predicated stores at sp + rank, the top one stays in registers (no per-child branches)
+#endif
+#ifndef POOL_POP2
+#define POOL_POP2 1     // pop loads two stack entries per iteration (both in flight before either is tested); 0: one
+#endif
 #ifndef POOL_SS
 #define POOL_SS 0       // entries of every ray's stack kept in shared memory (power of two, 0 = none); the rest lives in the global scratch.
                         // Measured on the stand-in (8 spp, ms per frame): 0 -> 79.4, 2 -> 85.8, 4 -> 86.7: the ring bookkeeping in the unrolled
@@ -142,6 +151,9 @@ __device__ __forceinline__ uint32_t pool_next(const PoolWarp& pw, uint32_t slot,
         if (has_top) {
             e = top, has_top = false;
         } else if (S::kShort) {
+            e = stk.pop();
+            if (__uint_as_float(e.y) > best_t) continue;  // ray_bvh_intersection.rs:40
+        } else if (!POOL_POP2) {
             e = stk.pop();
             if (__uint_as_float(e.y) > best_t) continue;  // ray_bvh_intersection.rs:40
         } else {
@@ -297,13 +309,42 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
                 bt = pw.f(PC_BT, slot);
                 const uint32_t node = pw.u(PC_PIDX, slot);
                 if (COUNT) tc.vis.inner++;
-                const bool nanpath = ray_needs_nanpath(r);
+                const bool nanpath = ray_needs_nanpath(sc, r);
                 RaySel sel{};
-                if (LAYOUT == MP_LAYOUT_DECODED && !nanpath) sel = ray_sel(r);
-                if (ORDER == MP_ORDER_REFERENCE) {
+                constexpr bool MIXED = POOL_MIXED && LAYOUT == MP_LAYOUT_QUANTISED;
+                if ((MIXED || LAYOUT == MP_LAYOUT_DECODED) && !nanpath) sel = ray_sel(r);
+                if (ORDER == MP_ORDER_REFERENCE && POOL_PUSH_RANK && !SHORT && (MIXED || LAYOUT == MP_LAYOUT_QUANTISED)) {
+                    // Every hit child but the highest lane goes to the stack at sp + (its rank among the hits), lanes ascending — the
+                    // order StackSink / PoolDeferSink produce — and the highest lane, which would be popped next and always survives the
+                    // `t1 > best.t` test (t1 <= t2 <= max_t = best.t), is handed to pool_advance in registers.
+                    uint32_t links[8];
+                    float t1s[8];
+                    uint32_t mask;
+                    if (nanpath)
+                        mask = inner_quantised_hits<true>(sc, r, node, bt, links, t1s);
+                    else if (MIXED)
+                        mask = inner_decoded256_hits(sc, r, sel, node, bt, links, t1s);
+                    else
+                        mask = inner_quantised_hits<false>(sc, r, node, bt, links, t1s);
+                    has_top = mask != 0u;
+                    uint2* dst = stk.spill + (size_t)stk.sp * POOL_W;
+#pragma unroll
+                    for (int lane = 0; lane < 8; ++lane) {
+                        const bool h = (mask >> lane) & 1u;
+                        const bool push = lane < 7 && h && (mask >> (lane + 1)) != 0u;  // a higher lane hit too: this one is not the top
+                        if (push) {
+                            *dst = make_uint2(links[lane], __float_as_uint(t1s[lane]));
+                            dst += POOL_W;
+                            ++stk.sp;
+                        }
+                        if (h) top = make_uint2(links[lane], __float_as_uint(t1s[lane]));
+                    }
+                } else if (ORDER == MP_ORDER_REFERENCE) {
                     PoolDeferSink<Stack> sink{stk, make_uint2(0u, 0u), false};
                     if (nanpath)
                         visit_inner<LAYOUT, true>(sc, r, sel, node, bt, sink);
+                    else if (MIXED)
+                        inner_decoded256(sc, r, sel, node, bt, sink);
                     else
                         visit_inner<LAYOUT, false>(sc, r, sel, node, bt, sink);
                     has_top = sink.has, top = sink.top;
@@ -443,7 +484,7 @@ __device__ __forceinline__ void pool_run_owned(const Scene& sc, uint32_t n, uint
                 const float bt = pw.f(PC_BT, slot);
                 const uint32_t node = pw.u(PC_PIDX, slot);
                 if (COUNT) tc.vis.inner++;
-                const bool nanpath = ray_needs_nanpath(r);
+                const bool nanpath = ray_needs_nanpath(sc, r);
                 RaySel sel{};
                 if (LAYOUT == MP_LAYOUT_DECODED && !nanpath) sel = ray_sel(r);
                 bool has_top = false;

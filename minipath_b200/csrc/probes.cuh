@@ -29,4 +29,45 @@ __global__ void __launch_bounds__(512) probe_l2_kernel(const uint4* __restrict__
     if (acc == 0x9e3779b9u) out[0] = acc;
 }
 
+// The same stream with 256-bit loads (ld.global.cg.v8: L2 only), for the sweep that looks for the highest L2 read rate.
+__global__ void __launch_bounds__(512) probe_l2_v8_kernel(const uint4* __restrict__ buf, size_t n_vec2, int passes, uint32_t* __restrict__ out) {
+    uint32_t acc = 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int p = 0; p < passes; ++p)
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec2; i += stride) {
+            uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
+            asm volatile("ld.global.cg.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7)
+                         : "l"(buf + 2 * i));
+            acc ^= r0 ^ r1 ^ r2 ^ r3 ^ r4 ^ r5 ^ r6 ^ r7;
+        }
+    if (acc == 0x9e3779b9u) out[0] = acc;
+}
+
+// L1 gather roof of an incoherent traversal: every lane fetches ITS OWN record (SECTORS x 32 bytes, 32-byte aligned, picked by a
+// per-lane LCG whose next state depends on the loaded data, like a traversal step) with 256-bit read-only loads.  The L1 pipe
+// serves such a warp-wide gather one 32-byte sector per lane and cycle whatever the records hold, so this rate — sectors per
+// second over the whole GPU — bounds any thread-per-node traversal (profiles/r1b_ubench_l1_patterns.txt, scripts/ubench/l1_patterns.cu).
+template <int SECTORS>
+__global__ void __launch_bounds__(128) probe_l1_gather_kernel(const uint4* __restrict__ recs, uint32_t n_recs, int iters, uint32_t* __restrict__ out) {
+    uint32_t seed = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
+    uint32_t acc = 0;
+    for (int it = 0; it < iters; ++it) {
+        seed = seed * 747796405u + 2891336453u;
+        const uint32_t w = ((seed >> ((seed >> 28) + 4u)) ^ seed) * 277803737u;
+        const uint32_t idx = ((w >> 22) ^ w) % n_recs;
+        const uint4* n = recs + (size_t)idx * (2 * SECTORS);
+#pragma unroll
+        for (int k = 0; k < SECTORS; ++k) {
+            uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
+            asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7)
+                         : "l"(n + 2 * k));
+            acc ^= r0 ^ r3 ^ r5 ^ r7;
+        }
+        seed ^= acc & 1u;
+    }
+    if (acc == 0x12345678u) out[0] = acc;
+}
+
 }  // namespace mpd

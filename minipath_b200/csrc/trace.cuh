@@ -31,6 +31,7 @@ struct Scene {
     const float4* __restrict__ packets_w;  // decoded packets, MPD_PACK_W float4 each
     uint32_t root;
     float eps;  // extension integrator: origin offset, 1e-4 * scene diagonal
+    uint32_t minmax_ok;  // every real child box has min <= max after dequantisation (checked by decode_inner_kernel at upload)
 };
 
 struct Hit {  // LeafHitRecord (ray_bvh_intersection.rs:165-171); the geometric normal is recomputed at finalise
@@ -134,8 +135,10 @@ __device__ __forceinline__ RaySel ray_sel(const Ray& r) {
     return s;
 }
 // Rays that need the reference's NaN handling (aabb.rs:262-267) or are not finite at all take the general path.
-__device__ __forceinline__ bool ray_needs_nanpath(const Ray& r) {
-    return !(fabsf(r.inv.x) < MPD_INF) | !(fabsf(r.inv.y) < MPD_INF) | !(fabsf(r.inv.z) < MPD_INF) | !(fabsf(r.o.x) < MPD_INF) |
+// So do all rays of a scene whose child boxes are not all min <= max (never the case for a builder-made BVH): the fast path picks
+// the near / far planes per ray, which presumes ordered boxes.
+__device__ __forceinline__ bool ray_needs_nanpath(const Scene& sc, const Ray& r) {
+    return !sc.minmax_ok | !(fabsf(r.inv.x) < MPD_INF) | !(fabsf(r.inv.y) < MPD_INF) | !(fabsf(r.inv.z) < MPD_INF) | !(fabsf(r.o.x) < MPD_INF) |
            !(fabsf(r.o.y) < MPD_INF) | !(fabsf(r.o.z) < MPD_INF);
 }
 
@@ -171,8 +174,77 @@ struct StackSink {
     }
 };
 // InnerNode::intersect on a quantised node record (ray_bvh_intersection.rs:149-162).
+//
+// MPD_INNER_SPLIT (default): the slab tests of the eight children are ONE straight-line block that ends in a hit mask, and the
+// hit children are handed to the sink afterwards, lanes ascending.  The first version tested and pushed child by child: a NULL
+// test, a branch around the test and a branch around the push per child — the compiler then re-materialised the dequantisation
+// constants behind every branch (6 of the 58 instructions a child cost, profiles/r2_sass_inner_before.txt) and could not
+// overlap the dependent chains of neighbouring children.  Same operations on the same operands, so the same bits.
+// MPD_QSEL: on the NaN-free path the near / far plane of every axis is known per RAY (sign of inv; needs min <= max per child,
+// Scene::minmax_ok), so the near and far rows are picked once per node with 24 selects instead of ordering lo / hi per child
+// with 48 min / max — what the decoded layout does with row offsets (RaySel).
+#ifndef MPD_INNER_SPLIT
+#define MPD_INNER_SPLIT 1
+#endif
+#ifndef MPD_QSEL
+#define MPD_QSEL 1
+#endif
+__device__ __forceinline__ uint4 sel4(bool c, const uint4& a, const uint4& b) { return make_uint4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w); }
+
+// Slab tests of the eight children of a quantised node record: returns the hit mask (bit = child lane), fills links and t1.
+template <bool NANPATH>
+__device__ __forceinline__ uint32_t inner_quantised_hits(const Scene& sc, const Ray& r, uint32_t index, float max_t, uint32_t (&links)[8], float (&t1s)[8]) {
+    const uint4* n = sc.inner_rec + 10 * (size_t)index;
+    uint4 q[6], la, lb, b0, b1;
+    ldg256(n + 0, q[0], q[1]);
+    ldg256(n + 2, q[2], q[3]);
+    ldg256(n + 4, q[4], q[5]);
+    ldg256(n + 6, la, lb);
+    ldg256(n + 8, b0, b1);
+    const F3 bmin = f3(__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b0.z));
+    const F3 bsize = f3(__uint_as_float(b1.x), __uint_as_float(b1.y), __uint_as_float(b1.z));
+    links[0] = la.x, links[1] = la.y, links[2] = la.z, links[3] = la.w, links[4] = lb.x, links[5] = lb.y, links[6] = lb.z, links[7] = lb.w;
+    uint32_t mask = 0u;
+    if (!NANPATH && MPD_QSEL) {
+        const bool sx = r.inv.x < 0.0f, sy = r.inv.y < 0.0f, sz = r.inv.z < 0.0f;
+        const uint4 nx = sel4(sx, q[3], q[0]), fx = sel4(sx, q[0], q[3]);
+        const uint4 ny = sel4(sy, q[4], q[1]), fy = sel4(sy, q[1], q[4]);
+        const uint4 nz = sel4(sz, q[5], q[2]), fz = sel4(sz, q[2], q[5]);
+#pragma unroll
+        for (int lane = 0; lane < 8; ++lane) {
+            const float lox = __fmul_rn(__fsub_rn(dequant(nx, lane, bsize.x, bmin.x), r.o.x), r.inv.x);
+            const float loy = __fmul_rn(__fsub_rn(dequant(ny, lane, bsize.y, bmin.y), r.o.y), r.inv.y);
+            const float loz = __fmul_rn(__fsub_rn(dequant(nz, lane, bsize.z, bmin.z), r.o.z), r.inv.z);
+            const float hix = __fmul_rn(__fsub_rn(dequant(fx, lane, bsize.x, bmin.x), r.o.x), r.inv.x);
+            const float hiy = __fmul_rn(__fsub_rn(dequant(fy, lane, bsize.y, bmin.y), r.o.y), r.inv.y);
+            const float hiz = __fmul_rn(__fsub_rn(dequant(fz, lane, bsize.z, bmin.z), r.o.z), r.inv.z);
+            const float t1 = fmaxf(fmaxf(lox, loy), fmaxf(loz, 0.0f));  // FMNMX3 + FMNMX
+            const float t2 = fminf(fminf(hix, hiy), fminf(hiz, max_t));
+            t1s[lane] = t1;
+            mask |= (t1 <= t2 && links[lane] != MP_LINK_NULL) ? (1u << lane) : 0u;
+        }
+    } else {
+#pragma unroll
+        for (int lane = 0; lane < 8; ++lane) {
+            float t1;
+            const bool hit = child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1);
+            t1s[lane] = t1;
+            mask |= (hit && links[lane] != MP_LINK_NULL) ? (1u << lane) : 0u;  // NULL: all-zero bounds, discarded when popped (:49); skipping is neutral
+        }
+    }
+    return mask;
+}
+
 template <bool NANPATH, class Sink>
 __device__ __forceinline__ void inner_quantised(const Scene& sc, const Ray& r, uint32_t index, float max_t, Sink& sink) {
+#if MPD_INNER_SPLIT
+    uint32_t links[8];
+    float t1s[8];
+    const uint32_t mask = inner_quantised_hits<NANPATH>(sc, r, index, max_t, links, t1s);
+#pragma unroll
+    for (int lane = 0; lane < 8; ++lane)
+        if (mask & (1u << lane)) sink.hit(links[lane], t1s[lane]);
+#else
     const uint4* n = sc.inner_rec + 10 * (size_t)index;
     uint4 q[6], la, lb, b0, b1;
     ldg256(n + 0, q[0], q[1]);
@@ -189,6 +261,7 @@ __device__ __forceinline__ void inner_quantised(const Scene& sc, const Ray& r, u
         float t1;
         if (child_slab<NANPATH>(q, lane, bmin, bsize, r, max_t, t1)) sink.hit(links[lane], t1);
     }
+#endif
 }
 
 // One quantised packet record: RelativeTriangle8::decompress + Triangle<WorldPoint8>::intersect (ray_bvh_intersection.rs:104-141).
@@ -244,6 +317,23 @@ __device__ __forceinline__ void inner_decoded(const Scene& sc, const Ray& r, con
         } else {
             const float4 ax = __ldg(n + sel.nx + h), ay = __ldg(n + sel.ny + h), az = __ldg(n + sel.nz + h);
             const float4 bx = __ldg(n + sel.fx + h), by = __ldg(n + sel.fy + h), bz = __ldg(n + sel.fz + h);
+#if MPD_INNER_SPLIT
+            float t1s[4];
+            uint32_t mask = 0u;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float lox = __fmul_rn(__fsub_rn(comp(ax, k), r.o.x), r.inv.x), loy = __fmul_rn(__fsub_rn(comp(ay, k), r.o.y), r.inv.y);
+                const float loz = __fmul_rn(__fsub_rn(comp(az, k), r.o.z), r.inv.z), hix = __fmul_rn(__fsub_rn(comp(bx, k), r.o.x), r.inv.x);
+                const float hiy = __fmul_rn(__fsub_rn(comp(by, k), r.o.y), r.inv.y), hiz = __fmul_rn(__fsub_rn(comp(bz, k), r.o.z), r.inv.z);
+                const float t1 = fmaxf(fmaxf(lox, loy), fmaxf(loz, 0.0f));    // FMNMX3 + FMNMX
+                const float t2 = fminf(fminf(hix, hiy), fminf(hiz, max_t));
+                t1s[k] = t1;
+                mask |= t1 <= t2 ? (1u << k) : 0u;  // NULL children: t1 = +inf, t2 = -inf
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (mask & (1u << k)) sink.hit(comp(lk, k), t1s[k]);
+#else
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const float lox = __fmul_rn(__fsub_rn(comp(ax, k), r.o.x), r.inv.x), loy = __fmul_rn(__fsub_rn(comp(ay, k), r.o.y), r.inv.y);
@@ -253,8 +343,48 @@ __device__ __forceinline__ void inner_decoded(const Scene& sc, const Ray& r, con
                 const float t2 = fminf(fminf(hix, hiy), fminf(hiz, max_t));
                 if (t1 <= t2) sink.hit(comp(lk, k), t1);  // NULL children: t1 = +inf, t2 = -inf
             }
+#endif
         }
     }
+}
+
+// Decoded node read with 256-bit loads (NaN-free rays only): a row pair (children 0-3, 4-7) of one plane is 32 contiguous bytes,
+// so the six near / far rows and the links are 7 x LDG.256 instead of 14 x LDG.128 — for incoherent gathers the request count is
+// what the L1 pipe charges (profiles/r1b_ubench_l1_patterns.txt).  Used by the pool kernels' MIXED layout: decoded inner nodes
+// (a few thousand nodes, cache-resident) with quantised triangle packets.
+__device__ __forceinline__ uint32_t inner_decoded256_hits(const Scene& sc, const Ray& r, const RaySel& sel, uint32_t index, float max_t, uint32_t (&links)[8], float (&t1s)[8]) {
+    const uint4* n = reinterpret_cast<const uint4*>(sc.inner_w + MPD_NODE_W * (size_t)index);
+    uint4 ax[2], ay[2], az[2], bx[2], by[2], bz[2], lk[2];
+    ldg256(n + sel.nx, ax[0], ax[1]);
+    ldg256(n + sel.ny, ay[0], ay[1]);
+    ldg256(n + sel.nz, az[0], az[1]);
+    ldg256(n + sel.fx, bx[0], bx[1]);
+    ldg256(n + sel.fy, by[0], by[1]);
+    ldg256(n + sel.fz, bz[0], bz[1]);
+    ldg256(n + 12, lk[0], lk[1]);
+    uint32_t mask = 0u;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const int h = c >> 2, k = c & 3;
+        const float lox = __fmul_rn(__fsub_rn(__uint_as_float(comp(ax[h], k)), r.o.x), r.inv.x), loy = __fmul_rn(__fsub_rn(__uint_as_float(comp(ay[h], k)), r.o.y), r.inv.y);
+        const float loz = __fmul_rn(__fsub_rn(__uint_as_float(comp(az[h], k)), r.o.z), r.inv.z), hix = __fmul_rn(__fsub_rn(__uint_as_float(comp(bx[h], k)), r.o.x), r.inv.x);
+        const float hiy = __fmul_rn(__fsub_rn(__uint_as_float(comp(by[h], k)), r.o.y), r.inv.y), hiz = __fmul_rn(__fsub_rn(__uint_as_float(comp(bz[h], k)), r.o.z), r.inv.z);
+        const float t1 = fmaxf(fmaxf(lox, loy), fmaxf(loz, 0.0f));
+        const float t2 = fminf(fminf(hix, hiy), fminf(hiz, max_t));
+        t1s[c] = t1;
+        links[c] = comp(lk[h], k);
+        mask |= t1 <= t2 ? (1u << c) : 0u;  // NULL children: t1 = +inf, t2 = -inf
+    }
+    return mask;
+}
+template <class Sink>
+__device__ __forceinline__ void inner_decoded256(const Scene& sc, const Ray& r, const RaySel& sel, uint32_t index, float max_t, Sink& sink) {
+    uint32_t links[8];
+    float t1s[8];
+    const uint32_t mask = inner_decoded256_hits(sc, r, sel, index, max_t, links, t1s);
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+        if (mask & (1u << c)) sink.hit(links[c], t1s[c]);
 }
 
 // One decoded packet: Triangle<WorldPoint8>::intersect + the t-range mask (triangle.rs:187-216; ray_bvh_intersection.rs:125-134).
@@ -344,7 +474,7 @@ __device__ __forceinline__ Hit trace_impl(const Scene& sc, const Ray& r, bool an
 template <int LAYOUT, int ORDER, bool COUNT>
 __device__ __forceinline__ Hit trace(const Scene& sc, const Ray& r, bool any_hit, Visits& vis) {
     // |inv| is infinite for a zero (or denormal) direction component
-    if (ray_needs_nanpath(r)) return trace_impl<LAYOUT, ORDER, COUNT, true>(sc, r, any_hit, vis);
+    if (ray_needs_nanpath(sc, r)) return trace_impl<LAYOUT, ORDER, COUNT, true>(sc, r, any_hit, vis);
     return trace_impl<LAYOUT, ORDER, COUNT, false>(sc, r, any_hit, vis);
 }
 

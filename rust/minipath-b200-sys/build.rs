@@ -23,11 +23,12 @@ fn main() {
     let inc = root.join("include");
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "/usr/local/cuda/bin/nvcc".into());
     let cxx = env::var("CXX").unwrap_or_else(|_| "g++".into());
-    let host = ["host_bvh", "host_camera", "host_render", "host_image"];
+    let host = ["host_bvh", "host_camera", "host_render", "host_image", "host_group"];
     for name in host {
         run(Command::new(&cxx)
             .args(["-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-c"])
             .arg(format!("-I{}", inc.display()))
+            .arg("-I/usr/local/cuda/include") // host_group.cpp: cuda_runtime_api.h (events, streams)
             .arg(cs.join(format!("{name}.cpp")))
             .arg("-o")
             .arg(out.join(format!("{name}.o"))));
@@ -44,7 +45,7 @@ fn main() {
     for name in host {
         link.arg(out.join(format!("{name}.o")));
     }
-    link.arg(out.join("context.o")).args(["-lpthread", "-lrt"]);
+    link.arg(out.join("context.o")).args(["-lpthread", "-lrt", "-ldl"]);
     run(&mut link);
     println!("cargo:rustc-link-search=native={}", out.display());
     println!("cargo:rustc-link-lib=dylib=minipath_b200");

@@ -41,6 +41,9 @@ pub const MP_TRACE_HYBRID_POOL_S0: u32 = 6;
 pub const MP_LAYOUT_QUANTISED: u32 = 0;
 pub const MP_LAYOUT_DECODED: u32 = 1;
 pub const MP_LAYOUT_AUTO: u32 = 2;
+pub const MP_SHARD_TILES: u32 = 0;
+pub const MP_SHARD_SPP: u32 = 1;
+pub const MP_NCCL_ID_BYTES: usize = 128;
 
 #[repr(C)]
 #[derive(Clone, Copy, Debug, Default)]
@@ -231,6 +234,10 @@ pub struct MpRenderProgress {
 pub struct MpTileQueue {
     _opaque: [u8; 0],
 }
+#[repr(C)]
+pub struct MpGroup {
+    _opaque: [u8; 0],
+}
 
 pub type MpStartedTileFn = Option<unsafe extern "C" fn(user: *mut c_void, tile: MpTile)>;
 pub type MpFinishedTileFn = Option<unsafe extern "C" fn(user: *mut c_void, tile: MpTile, progress: MpProgressSnapshot)>;
@@ -268,6 +275,7 @@ extern "C" {
     pub fn mp_ctx_pool_clear() -> c_int;
     pub fn mp_ctx_set_stream(ctx: *mut MpCtx, cuda_stream: *mut c_void) -> c_int;
     pub fn mp_ctx_sync(ctx: *mut MpCtx) -> c_int;
+    pub fn mp_ctx_stream(ctx: *mut MpCtx, out_cuda_stream: *mut *mut c_void) -> c_int;
     pub fn mp_ctx_set_trace_variant(ctx: *mut MpCtx, variant: u32) -> c_int;
     pub fn mp_ctx_set_node_layout(ctx: *mut MpCtx, layout: u32) -> c_int;
     pub fn mp_ctx_enable_counters(ctx: *mut MpCtx, on: c_int) -> c_int;
@@ -276,6 +284,8 @@ extern "C" {
     pub fn mp_last_device_ms(ctx: *mut MpCtx, out_ms: *mut f32) -> c_int;
     pub fn mp_probe_fp32_tflops(ctx: *mut MpCtx, out_tflops: *mut f32) -> c_int;
     pub fn mp_probe_l2_gbs(ctx: *mut MpCtx, bytes: usize, out_gbs: *mut f32) -> c_int;
+    pub fn mp_probe_l2_gbs_shape(ctx: *mut MpCtx, bytes: usize, blocks_per_sm: u32, vec_bytes: u32, out_gbs: *mut f32) -> c_int;
+    pub fn mp_probe_l1_gather(ctx: *mut MpCtx, n_records: u32, sectors_per_record: u32, out_gsectors_per_s: *mut f32) -> c_int;
 
     // scene, camera, film
     pub fn mp_scene_upload(ctx: *mut MpCtx, bvh: *const MpFlatBvh) -> c_int;
@@ -328,7 +338,28 @@ extern "C" {
     pub fn mp_tileq_open(name: *const c_char, create: c_int, out: *mut *mut MpTileQueue) -> c_int;
     pub fn mp_tileq_reset(q: *mut MpTileQueue) -> c_int;
     pub fn mp_tileq_next(q: *mut MpTileQueue, batch: u64, out_first: *mut u64) -> c_int;
+    pub fn mp_tileq_peek(q: *mut MpTileQueue, out_next: *mut u64) -> c_int;
+    pub fn mp_tileq_barrier(q: *mut MpTileQueue, world: u32, timeout_ms: u32) -> c_int;
     pub fn mp_tileq_close(q: *mut MpTileQueue, unlink: c_int) -> c_int;
+
+    // multi-GPU groups (machinery.rs:51-116,205-209 over the GPUs of one box; NCCL film reduce)
+    pub fn mp_group_create(devices: *const c_int, n_devices: c_int, out: *mut *mut MpGroup) -> c_int;
+    pub fn mp_group_unique_id(out: *mut u8) -> c_int;
+    pub fn mp_group_create_rank(device: c_int, rank: c_int, world: c_int, id: *const u8, queue_name: *const c_char, out: *mut *mut MpGroup) -> c_int;
+    pub fn mp_group_destroy(g: *mut MpGroup) -> c_int;
+    pub fn mp_group_size(g: *mut MpGroup, out_local: *mut c_int, out_world: *mut c_int) -> c_int;
+    pub fn mp_group_ctx(g: *mut MpGroup, local_index: c_int, out: *mut *mut MpCtx) -> c_int;
+    pub fn mp_group_scene_upload(g: *mut MpGroup, bvh: *const MpFlatBvh) -> c_int;
+    pub fn mp_group_camera_set(g: *mut MpGroup, sampler: *const MpCameraSampler) -> c_int;
+    pub fn mp_group_set_trace_variant(g: *mut MpGroup, variant: u32) -> c_int;
+    pub fn mp_group_film_create(g: *mut MpGroup, width: u32, height: u32) -> c_int;
+    pub fn mp_group_render(g: *mut MpGroup, tiles: *const MpTile, n_tiles: u32, params: *const MpRenderParams, shard: u32, min_batch: u32) -> c_int;
+    pub fn mp_group_reduce_film(g: *mut MpGroup) -> c_int;
+    pub fn mp_group_resolve_rgba8(g: *mut MpGroup, spp_total: u32, host_out: *mut u8) -> c_int;
+    pub fn mp_group_read_film(g: *mut MpGroup, local_index: c_int, host_out: *mut f32) -> c_int;
+    pub fn mp_group_sync(g: *mut MpGroup) -> c_int;
+    pub fn mp_group_last_ms(g: *mut MpGroup, out_ms: *mut f32) -> c_int;
+    pub fn mp_group_member_stats(g: *mut MpGroup, local_index: c_int, out_batches: *mut u64, out_tiles: *mut u64, out_ms: *mut f32) -> c_int;
 }
 
 /// The library's thread-local message for the last failed call on this thread.

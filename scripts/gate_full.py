@@ -1,0 +1,174 @@
+#!/usr/bin/env python
+"""The parity gates at their STATED size (BASELINE.json configs[1], SURVEY §8(c) gates 1-3), run once per round on a B200:
+
+    gpurun ... -- 'bash scripts/gpu.sh gates'            # everything, about 10 minutes of box time
+    python scripts/gate_full.py --only bitexact --spp 64 # one gate
+
+  gate 1  bit-exact: cube and teapot at 1920x1080 x 64 spp = 132.7 M primary rays each; rays from the device ray-gen, traced by the
+          CUDA path (through the C ABI: mp_generate_rays + mp_trace_rays) and by the CPU oracle; triangle index and the bits of t
+          (and u, v) must agree for every ray: 0 mismatches.
+  gate 2  converged image: 4096 spp, independent seeds on the two sides, f32 films before quantisation: mean per-channel relative
+          error <= 0.5 %.  Teapot at 480x270 (reference shader and 5 bounces), cube at 480x270, stand-in at 240x136 with 5 bounces.
+  gate 3  equal spp: per-pixel Welch statistic over K = 32 batches of 32 samples at 320x180, fraction of pixels beyond |t| = 4 <= 3e-3.
+
+The oracle is the checker here, never the thing measured.  Output lines are kept in profiles/r2_gates.txt.
+"""
+import argparse
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import minipath_b200 as mp  # noqa: E402
+from oracle_lib import Oracle  # noqa: E402
+
+DATA = os.path.join(ROOT, "data")
+
+
+def scenes(names):
+    out = {}
+    if "teapot" in names:
+        out["teapot"] = (mp.TriangleBvh.with_obj(os.path.join(DATA, "teapot.obj")),
+                         mp.Camera.default().look_at((0, 2, 10), (0, 1.5, 0), (0, 1, 0)).f_number(4.8).focus_distance(10.0))
+    if "cube" in names:
+        out["cube"] = (mp.TriangleBvh.with_obj(os.path.join(DATA, "cube.obj"), quad_mode=1),
+                       mp.Camera.default().look_at((1.5, 1.2, 2.5), (0, 0, 0), (0, 1, 0)).f_number(64.0))
+    if "atrium" in names:
+        from minipath_b200 import scenes as sc
+
+        out["atrium"] = sc.atrium_scene()
+    return out
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def gate_bitexact(ctx, oracle, name, bvh, cam, w, h, spp, chunk_spp, threads):
+    """Gate 1 in chunks of `chunk_spp` samples per pixel (a chunk of 1080p x 8 spp is 16.6 M rays = 600 MB of rays)."""
+    sampler = cam.build_sampler((w, h))
+    ctx.upload_scene(bvh)
+    ctx.set_camera(sampler)
+    ctx.create_film(w, h)
+    tiles = mp.full_screen_tiles(w, h, 64, seed=9)
+    total = mism_tri = mism_t = mism_uv = hits = 0
+    t0 = time.time()
+    for base in range(0, spp, chunk_spp):
+        n = min(chunk_spp, spp - base)
+        st = mp.RenderSettings(64, n, (w, h), seed=1234)
+        rays = ctx.generate_rays(tiles, st.params(sample_base=base))            # device ray-gen (sample_ray + Ray::new)
+        r_cpu = oracle.generate_rays(sampler, w, tiles, st.params(sample_base=base))
+        if not np.array_equal(bits(rays), bits(r_cpu)):
+            raise SystemExit(f"gate 1 {name}: device rays differ from the oracle's rays in chunk {base}")
+        del r_cpu
+        h_gpu = ctx.trace_rays(rays, mp.ORDER_REFERENCE)
+        h_cpu = oracle.trace_rays(bvh, rays, mp.ORDER_REFERENCE, threads=threads)
+        total += len(rays)
+        hits += int((h_cpu["tri"] != mp.NO_HIT).sum())
+        mism_tri += int((h_gpu["tri"] != h_cpu["tri"]).sum())
+        mism_t += int((bits(h_gpu["t"]) != bits(h_cpu["t"])).sum())
+        mism_uv += int(((bits(h_gpu["u"]) != bits(h_cpu["u"])) | (bits(h_gpu["v"]) != bits(h_cpu["v"]))).sum())
+    ok = mism_tri == 0 and mism_t == 0 and mism_uv == 0
+    print(f"gate1 bit-exact {name:7s} {w}x{h}x{spp}spp: {total} primary rays, {hits} hits, mismatches tri={mism_tri} t={mism_t} uv={mism_uv} "
+          f"-> {'PASS' if ok else 'FAIL'}  ({time.time() - t0:.0f} s)", flush=True)
+    return ok
+
+
+def film(side, oracle, ctx, bvh, sampler, w, h, tiles, spp, seed, bounces, threads):
+    st = mp.RenderSettings(32, spp, (w, h), max_bounces=bounces, seed=seed, mode=mp.MODE_WAVEFRONT if bounces else mp.MODE_MEGAKERNEL)
+    if side == "gpu":
+        ctx.clear_film()
+        ctx.render_tiles(tiles, st.params())
+        return ctx.read_film()
+    return oracle.render_tiles(bvh, sampler, w, h, tiles, st.params(), threads=threads)[0]
+
+
+def gate_converged(ctx, oracle, name, bvh, cam, w, h, spp, bounces, threads):
+    sampler = cam.build_sampler((w, h))
+    ctx.upload_scene(bvh)
+    ctx.set_camera(sampler)
+    ctx.create_film(w, h)
+    ctx.set_trace_variant(mp.TRACE_HYBRID_POOL_S0 if bounces else mp.TRACE_THREAD)
+    tiles = mp.full_screen_tiles(w, h, 32, seed=1)
+    t0 = time.time()
+    fg = film("gpu", oracle, ctx, bvh, sampler, w, h, tiles, spp, 1001, bounces, threads).astype(np.float64) / spp
+    fc = film("cpu", oracle, ctx, bvh, sampler, w, h, tiles, spp, 2002, bounces, threads).astype(np.float64) / spp
+    rels = []
+    for ch in range(4):
+        denom = np.abs(fc[..., ch]).mean()
+        rels.append(np.abs(fg[..., ch] - fc[..., ch]).mean() / max(denom, 1e-12))
+    u8g, u8c = np.clip(np.floor(fg * 255 + 0.5), 0, 255), np.clip(np.floor(fc * 255 + 0.5), 0, 255)
+    du8 = np.abs(u8g - u8c)
+    ok = max(rels) <= 0.005
+    print(f"gate2 converged {name:7s} {w}x{h}x{spp}spp bounces={bounces}: mean rel err per channel " + " ".join(f"{r:.4%}" for r in rels)
+          + f" (tolerance 0.5 %); u8 mean |diff| {du8.mean():.3f}, within 1 code {(du8 <= 1).mean():.4f} -> {'PASS' if ok else 'FAIL'}  ({time.time() - t0:.0f} s)", flush=True)
+    return ok
+
+
+def gate_equal_spp(ctx, oracle, name, bvh, cam, w, h, n, K, bounces, threads):
+    sampler = cam.build_sampler((w, h))
+    ctx.upload_scene(bvh)
+    ctx.set_camera(sampler)
+    ctx.create_film(w, h)
+    ctx.set_trace_variant(mp.TRACE_HYBRID_POOL_S0 if bounces else mp.TRACE_THREAD)
+    tiles = mp.full_screen_tiles(w, h, 32, seed=1)
+    t0 = time.time()
+    g = np.stack([film("gpu", oracle, ctx, bvh, sampler, w, h, tiles, n, 100 + k, bounces, threads)[..., 0] / n for k in range(K)]).astype(np.float64)
+    c = np.stack([film("cpu", oracle, ctx, bvh, sampler, w, h, tiles, n, 500 + k, bounces, threads)[..., 0] / n for k in range(K)]).astype(np.float64)
+    mg, mc = g.mean(0), c.mean(0)
+    se = np.sqrt(g.var(0, ddof=1) / K + c.var(0, ddof=1) / K)
+    flat = se == 0
+    flat_ok = np.array_equal(mg[flat], mc[flat])
+    z = np.abs(mg[~flat] - mc[~flat]) / se[~flat]
+    frac = float((z > 4).mean()) if z.size else 0.0
+    ok = flat_ok and frac <= 3e-3
+    print(f"gate3 equal-spp {name:7s} {w}x{h}, {K} batches x {n} spp, bounces={bounces}: {int((z > 4).sum())} of {z.size} pixels beyond |t|=4 "
+          f"(fraction {frac:.2e}, tolerance 3e-3), zero-variance pixels equal: {flat_ok} -> {'PASS' if ok else 'FAIL'}  ({time.time() - t0:.0f} s)", flush=True)
+    return ok
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default="", choices=["", "bitexact", "converged", "equal"])
+    ap.add_argument("--spp", type=int, default=64, help="gate 1 samples per pixel (64 = the stated size)")
+    ap.add_argument("--chunk-spp", type=int, default=8)
+    ap.add_argument("--conv-spp", type=int, default=4096)
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink gate 2/3 resolutions (smoke runs)")
+    args = ap.parse_args()
+    if mp.device_count() == 0:
+        raise SystemExit("gate_full.py needs a B200 (no CPU fallback)")
+    threads = len(os.sched_getaffinity(0))
+    oracle = Oracle()
+    oracle.o.orc_set_simd(1)
+    ctx = mp.Context(0)
+    sc = scenes(["teapot", "cube", "atrium"])
+    ok = True
+    print(f"# full-size parity gates, {threads} host threads for the oracle, device 0", flush=True)
+    if args.only in ("", "bitexact"):
+        for variant, label in ((mp.TRACE_THREAD, "thread"), (mp.TRACE_POOL, "pool")):
+            ctx.set_trace_variant(variant)
+            for name in ("cube", "teapot"):
+                print(f"# traversal kernel: {label}", flush=True)
+                ok &= gate_bitexact(ctx, oracle, name, *sc[name], 1920, 1080, args.spp if variant == mp.TRACE_THREAD else min(args.spp, 8), args.chunk_spp, threads)
+    s = args.scale
+    if args.only in ("", "converged"):
+        ok &= gate_converged(ctx, oracle, "teapot", *sc["teapot"], int(480 * s), int(270 * s), args.conv_spp, 0, threads)
+        ok &= gate_converged(ctx, oracle, "teapot", *sc["teapot"], int(480 * s), int(270 * s), args.conv_spp, 5, threads)
+        ok &= gate_converged(ctx, oracle, "cube", *sc["cube"], int(480 * s), int(270 * s), args.conv_spp, 5, threads)
+        ok &= gate_converged(ctx, oracle, "atrium", *sc["atrium"], int(240 * s), int(136 * s), args.conv_spp, 5, threads)
+    if args.only in ("", "equal"):
+        ok &= gate_equal_spp(ctx, oracle, "teapot", *sc["teapot"], int(320 * s), int(180 * s), 32, 32, 0, threads)
+        ok &= gate_equal_spp(ctx, oracle, "atrium", *sc["atrium"], int(320 * s), int(180 * s), 32, 32, 5, threads)
+    ctx.close()
+    print("ALL GATES PASS" if ok else "SOME GATE FAILED", flush=True)
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
