@@ -28,7 +28,7 @@ HOST_OBJS := $(CS)/host_bvh.o $(CS)/host_camera.o $(CS)/host_render.o $(CS)/host
 $(LIB): $(HOST_OBJS) $(CS)/context.o
 	$(NVCC) -shared -o $@ $^ -lpthread -lrt -ldl -cudart static
 
-$(ORACLE): oracle/oracle.cpp oracle/oracle_trace.inc oracle/oracle_render.inc oracle/oracle.h include/minipath_b200.h
+$(ORACLE): oracle/oracle.cpp oracle/oracle_trace.inc oracle/oracle_render.inc oracle/oracle_build.inc oracle/oracle.h include/minipath_b200.h
 	$(CXX) -O2 -std=c++17 -fPIC -shared -mavx2 -mfma -ffp-contract=off -Wall -o $@ oracle/oracle.cpp -lpthread
 
 clean:

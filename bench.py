@@ -173,9 +173,37 @@ def host_cores():
 # ------------------------------------------------------------------------------------------------------------------
 # CPU arms (the oracle is test infrastructure: it runs ONLY here, as the thing beside the measurement, never inside it)
 # ------------------------------------------------------------------------------------------------------------------
+def oracle_workload(oracle, name, args):
+    """The workload on the CHECKER's side only: its own OBJ loader / mesh builder (oracle/oracle_build.inc), its own camera sampler
+    and tile list — nothing from libminipath_b200.so, which a CPU arm therefore never maps."""
+    from oracle_lib import scenes
+
+    scene, w, h, spp, bounces = workload_params(name, args)
+    data = os.path.join(ROOT, "data")
+    if scene == "teapot":  # camera of benches/render_teapot.rs:12-19
+        bvh = oracle.build_obj(os.path.join(data, "teapot.obj"))
+        sampler = oracle.camera_sampler((0, 2, 10), (0, 1.5, 0), (0, 1, 0), (w, h), f_number=4.8, focus_distance=10.0)
+    elif scene == "cube":
+        bvh = oracle.build_obj(os.path.join(data, "cube.obj"), quad_mode=1)
+        sampler = oracle.camera_sampler((1.5, 1.2, 2.5), (0, 0, 0), (0, 1, 0), (w, h), f_number=64.0, focus_distance=float(np.linalg.norm([1.5, 1.2, 2.5])))
+    else:
+        p, n, t = scenes.atrium_mesh()
+        bvh = oracle.build_mesh(p, t, n)
+        c = scenes.atrium_camera_params(*bvh.get_bounding_box())
+        sampler = oracle.camera_sampler(c["eye"], c["target"], c["up"], (w, h), sensor_size=c["sensor_width"], sensor_is_width=True,
+                                        focal_length=c["focal_length"], f_number=c["f_number"], focus_distance=c["focus"])
+    return bvh, sampler, oracle.tiles(w, h, 64), w, h, spp, bounces
+
+
+def render_params(spp, bounces, seed=7):
+    from oracle_lib import _ffi
+
+    return _ffi.MpRenderParams(spp, 0, bounces, 0, 0, 64, seed)
+
+
 def oracle_frame(oracle, bvh, sampler, w, h, tiles, params, threads):
     """One bounded frame on the CPU oracle; returns (seconds, rays, camera samples)."""
-    from minipath_b200 import _ffi
+    from oracle_lib import _ffi
 
     c = _ffi.MpCounters()
     film, secs, c = oracle.render_tiles(bvh, sampler, w, h, tiles, params, threads=threads, counters=c)
@@ -184,10 +212,7 @@ def oracle_frame(oracle, bvh, sampler, w, h, tiles, params, threads):
 
 def bounded_spp(oracle, bvh, sampler, w, h, tiles, bounces, spp, threads, seconds):
     """How many of the workload's spp fit `seconds` of oracle work (calibrated with one 1-spp frame)."""
-    import minipath_b200 as mp
-
-    st1 = mp.RenderSettings(64, 1, (w, h), max_bounces=bounces, seed=7)
-    s1, _, _ = oracle_frame(oracle, bvh, sampler, w, h, tiles, st1.params(), threads)
+    s1, _, _ = oracle_frame(oracle, bvh, sampler, w, h, tiles, render_params(1, bounces), threads)
     return int(max(1, min(spp, round(seconds / max(s1, 1e-3)))))
 
 
@@ -196,22 +221,18 @@ def run_reference(args, rank, world):
     workload, metric and config object; each step is a bounded sample: the full frame at `sample_spp` of the workload's spp."""
     if rank != 0:
         return
-    import minipath_b200 as mp
     from oracle_lib import Oracle
 
-    bvh, cam, w, h, spp, bounces = load_workload(args.workload, args)
     oracle = Oracle()
     oracle.o.orc_set_simd(1)
     threads = host_cores()
-    sampler = cam.build_sampler((w, h))
-    tiles = mp.full_screen_tiles(w, h, 64)
+    bvh, sampler, tiles, w, h, spp, bounces = oracle_workload(oracle, args.workload, args)
     n = bounded_spp(oracle, bvh, sampler, w, h, tiles, bounces, spp, threads, args.ref_seconds)
-    st = mp.RenderSettings(64, n, (w, h), max_bounces=bounces, seed=7)
     for _ in range(min(args.warmup, 1)):  # the calibration frame has already warmed caches and threads
-        oracle_frame(oracle, bvh, sampler, w, h, tiles, st.params(), threads)
+        oracle_frame(oracle, bvh, sampler, w, h, tiles, render_params(n, bounces), threads)
     secs = rays = samples = 0
     for _ in range(args.steps):
-        s, r, c = oracle_frame(oracle, bvh, sampler, w, h, tiles, st.params(), threads)
+        s, r, c = oracle_frame(oracle, bvh, sampler, w, h, tiles, render_params(n, bounces), threads)
         secs, rays, samples = secs + s, rays + r, samples + c
     mrays = rays / secs / 1e6
     sample = f"{args.workload}: full {w}x{h} frame at {n} of {spp} spp per step, {bounces} bounces, AVX2+FMA oracle, {threads} threads"
@@ -221,7 +242,9 @@ def run_reference(args, rank, world):
         "scaling": "strong" if args.shard == "tiles" else "weak", "vs_baseline": None, "dtype": "f32", "data": data_note(args.workload),
         "samples_per_s": samples / secs, "config": workload_config(args.workload, args),
         "sample": sample, "sample_spp": n,
-        "reference_kind": "CPU restatement of the reference path (oracle port; cargo/rustc absent), thread per core, atomic tile queue",
+        "reference_kind": "CPU restatement of the reference path (oracle port; cargo/rustc absent), thread per core, atomic tile queue; "
+                          "scene from the oracle's own loader + builder, libminipath_b200.so not loaded",
+        "product_library_loaded": "minipath_b200" in sys.modules,
         "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -229,19 +252,16 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def cpu_baseline(args, name, bvh, cam, w, h, spp, bounces):
+def cpu_baseline(args, name):
     """Oracle on the host cores, bounded to roughly 10-20 s: 1 spp to calibrate, then as many spp as fit."""
-    import minipath_b200 as mp
     from oracle_lib import Oracle
 
     oracle = Oracle()
     oracle.o.orc_set_simd(1)
     threads = host_cores()
-    sampler = cam.build_sampler((w, h))
-    tiles = mp.full_screen_tiles(w, h, 64)
+    bvh, sampler, tiles, w, h, spp, bounces = oracle_workload(oracle, name, args)
     n = bounded_spp(oracle, bvh, sampler, w, h, tiles, bounces, spp, threads, args.ref_seconds)
-    st = mp.RenderSettings(64, n, (w, h), max_bounces=bounces, seed=7)
-    secs, rays, samples = oracle_frame(oracle, bvh, sampler, w, h, tiles, st.params(), threads)
+    secs, rays, samples = oracle_frame(oracle, bvh, sampler, w, h, tiles, render_params(n, bounces), threads)
     return {"value": rays / secs / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port", "samples_per_s": samples / secs,
             "seconds": secs, "sample": f"{name}: full {w}x{h} frame at {n} of {spp} spp, {bounces} bounces, AVX2+FMA oracle, {threads} threads"}
 
@@ -632,7 +652,7 @@ def main():
         rl = roofline(args, res, probes)
         cb = None
         if world == 1 and not args.no_cpu_baseline:
-            cb = cpu_baseline(args, args.workload, res["bvh"], res["cam"], res["w"], res["h"], res["spp"], res["bounces"])
+            cb = cpu_baseline(args, args.workload)
         extra = None
         if world == 1 and not args.no_extra and args.workload == DEFAULT_WORKLOAD:
             r2 = measure_single(args, "teapot-1080p", torch, local, full=False)

@@ -35,9 +35,7 @@ from ._ffi import (  # noqa: F401  (re-exported)
     lib,
 )
 
-RAY_DTYPE = np.dtype([("origin", "<f4", 3), ("direction", "<f4", 3), ("inv_direction", "<f4", 3)])
-HIT_DTYPE = np.dtype([("tri", "<u4"), ("t", "<f4"), ("u", "<f4"), ("v", "<f4")])
-TILE_DTYPE = np.dtype([("min_x", "<u4"), ("min_y", "<u4"), ("max_x", "<u4"), ("max_y", "<u4")])
+from ._abi_types import HIT_DTYPE, RAY_DTYPE, TILE_DTYPE  # noqa: E402,F401
 
 
 def _f3(v):
@@ -104,12 +102,8 @@ class ScreenBlock:
         return self.min[0] <= p[0] < self.max[0] and self.min[1] <= p[1] < self.max[1]
 
     def internal_points(self):
-        """(x, y) pairs in C order, x fastest (screen_block.rs:28-39,104-128)."""
-        if self.is_empty():
-            return
-        for y in range(self.min[1], self.max[1]):
-            for x in range(self.min[0], self.max[0]):
-                yield (x, y)
+        """Iterator over the (x, y) pairs inside the block in C order, x fastest; exact length at every step (screen_block.rs:28-39,84-143)."""
+        return InternalPoints(self)
 
     def tile_ordering(self, tile_size, seed=0):
         """Tiles of tile_size (clipped at the right/bottom), centre-out with Exp noise (screen_block.rs:46-81)."""
@@ -124,6 +118,34 @@ class ScreenBlock:
 
     def __repr__(self):
         return f"ScreenBlock({self.min}, {self.max})"
+
+
+class InternalPoints:
+    """screen_block.rs:84-143: a cursor over the block, an ExactSizeIterator (``len()`` is exact before and during iteration)."""
+
+    def __init__(self, block):
+        if block.is_empty():  # InternalPoints::empty (:92-101)
+            self.min_x, self.max, self.cursor = 1, (0, 0), [0, 0]
+        else:
+            self.min_x, self.max, self.cursor = block.min[0], block.max, [block.min[0], block.min[1]]
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        if self.cursor[1] >= self.max[1]:
+            raise StopIteration
+        ret = (self.cursor[0], self.cursor[1])
+        self.cursor[0] += 1
+        if self.cursor[0] >= self.max[0]:
+            self.cursor[0] = self.min_x
+            self.cursor[1] += 1
+        return ret
+
+    def __len__(self):
+        if self.cursor[1] >= self.max[1]:
+            return 0
+        return (self.max[1] - self.cursor[1] - 1) * (self.max[0] - self.min_x) + (self.max[0] - self.cursor[0])
 
 
 def tile_ordering_array(min_x, min_y, max_x, max_y, tile_size, seed=0):

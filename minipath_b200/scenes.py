@@ -95,10 +95,8 @@ def atrium_mesh():
     return m.arrays()
 
 
-def atrium_camera(bbox_min, bbox_max):
-    """camera defined relative to the bounding box so that it survives the stand-in."""
-    from . import Camera
-
+def atrium_camera_params(bbox_min, bbox_max):
+    """camera defined relative to the bounding box so that it survives the stand-in (plain numbers, no library)."""
     lo, hi = np.asarray(bbox_min, np.float64), np.asarray(bbox_max, np.float64)
     c, s = 0.5 * (lo + hi), hi - lo
     long_axis = 0 if s[0] >= s[2] else 2
@@ -106,10 +104,16 @@ def atrium_camera(bbox_min, bbox_max):
     el[long_axis] = 1.0
     eye = c - 0.30 * s[long_axis] * el - 0.15 * s[1] * ey
     target = c + 0.30 * s[long_axis] * el - 0.10 * s[1] * ey
-    focus = float(np.linalg.norm(target - eye))
-    cam = (Camera.default().sensor_width(0.036).focal_length(0.024).f_number(16.0).focus_distance(focus)
-           .look_at(tuple(eye), tuple(target), (0.0, 1.0, 0.0)))
-    return cam
+    return {"eye": tuple(eye), "target": tuple(target), "up": (0.0, 1.0, 0.0), "focus": float(np.linalg.norm(target - eye)),
+            "sensor_width": 0.036, "focal_length": 0.024, "f_number": 16.0}
+
+
+def atrium_camera(bbox_min, bbox_max):
+    from . import Camera
+
+    p = atrium_camera_params(bbox_min, bbox_max)
+    return (Camera.default().sensor_width(p["sensor_width"]).focal_length(p["focal_length"]).f_number(p["f_number"]).focus_distance(p["focus"])
+            .look_at(p["eye"], p["target"], p["up"]))
 
 
 _ATRIUM_CACHE = {}

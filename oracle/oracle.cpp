@@ -8,6 +8,7 @@
 #include <atomic>
 #include <chrono>
 #include <cmath>
+#include <algorithm>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -172,3 +173,4 @@ int orc_get_simd(void) { return g_simd.load(); }
 
 #include "oracle_trace.inc"
 #include "oracle_render.inc"
+#include "oracle_build.inc"

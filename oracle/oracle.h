@@ -11,8 +11,10 @@
  *     encoding (triangle_bvh/mod.rs:189-236), bit_iter (util/mod.rs:40-56), camera orientation
  *     (camera.rs:200-226), fma_dot/fma_cross vs unfused (util/simba.rs:127-176).
  *   - PARITY UNPINNED (no reference test, golden vector or runnable reference exists): Triangle8::intersect,
- *     TriangleBvh::intersect, hit finalisation, render_tile / color_to_image.  There the oracle IS the
- *     restatement.  The reference RNG is OS-seeded (worker.rs:25), so no seed-exact image exists even
+ *     TriangleBvh::intersect, hit finalisation, render_tile / color_to_image, the builder.  There the oracle IS the
+ *     restatement.  What narrows the gap (tests/test_independent.py): the traversal is checked against a brute-force closest
+ *     hit over all packets and against plain numpy Moller-Trumbore on the SOURCE mesh; the builder (oracle_build.inc) and the
+ *     product's builder are two separate restatements that must agree byte for byte and satisfy the format's invariants.  The reference RNG is OS-seeded (worker.rs:25), so no seed-exact image exists even
  *     reference-vs-reference; oracle and CUDA share a counter-based RNG (below) so that they can be compared
  *     bit for bit.
  *   - max_bounces > 0 is an extension with no reference behaviour at all.
@@ -92,6 +94,23 @@ double orc_render_tiles(const MpFlatBvh* bvh, const MpCameraSampler* cam, uint32
                         MpCounters* counters, int threads);
 /* pixel_sum*(1/spp) + color_to_image for the whole film (worker.rs:44,69-76) */
 void orc_resolve_rgba8(const float* film, uint32_t width, uint32_t height, uint32_t spp_total, uint8_t* out);
+
+/* ---- scene sources and checks that do not share code with the product (oracle_build.inc) ---- */
+/* TriangleBvh::with_obj / build (building.rs:28-207,238-450) restated on its own; quad_mode 1 fan-triangulates polygons.
+ * Returns 0, or -1 with orc_build_error() where the reference would panic.  The arrays carry the box tables too, so the same
+ * MpFlatBvh can be uploaded to the GPU: the device then traverses a tree the product did not build. */
+int orc_bvh_build_obj(const char* path, int quad_mode, MpFlatBvh** out);
+int orc_bvh_build_mesh(const float* positions, const float* normals, uint32_t n_vertices, const uint32_t* triangles,
+                       uint64_t n_triangles, MpFlatBvh** out);
+void orc_bvh_free(MpFlatBvh* bvh);
+const char* orc_build_error(void);
+/* Closest hit over ALL packets with Triangle8::intersect, no inner nodes, no traversal (lowest triangle index among equal t). */
+void orc_brute_force(const MpFlatBvh* bvh, const MpRay* rays, uint64_t n, MpHit* out, int threads);
+/* Camera::look_at + build_sampler (camera.rs:93-116,123-146) and a row-major tile list (screen_block.rs:46-60,146-160): what the
+ * CPU arms of bench.py need to run without mapping the product library. */
+void orc_camera_sampler(const float center[3], const float target[3], const float up_hint[3], float sensor_size, int sensor_is_width,
+                        float focal_length, float f_number, float focus_distance, uint32_t res_x, uint32_t res_y, MpCameraSampler* out);
+uint32_t orc_tiles(uint32_t width, uint32_t height, uint32_t tile_size, MpTile* out, uint32_t cap);
 
 #ifdef __cplusplus
 }

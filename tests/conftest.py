@@ -22,18 +22,33 @@ def oracle():
     return Oracle()
 
 
+# Scenes of the parity tests come from the ORACLE's own loader and builder (oracle/oracle_build.inc), not from the product's: the
+# GPU then traverses a tree the code under test did not build, and both sides of every comparison read the same arrays.  That the
+# product's builder makes byte-identical arrays is a separate CPU test (tests/test_independent.py).
 @pytest.fixture(scope="session")
-def teapot():
-    import minipath_b200 as mp
-
-    return mp.TriangleBvh.with_obj(os.path.join(DATA, "teapot.obj"))
+def teapot(oracle):
+    return oracle.build_obj(os.path.join(DATA, "teapot.obj"))
 
 
 @pytest.fixture(scope="session")
-def cube():
-    import minipath_b200 as mp
+def cube(oracle):
+    return oracle.build_obj(os.path.join(DATA, "cube.obj"), quad_mode=1)
 
-    return mp.TriangleBvh.with_obj(os.path.join(DATA, "cube.obj"), quad_mode=1)
+
+@pytest.fixture(scope="session")
+def atrium(oracle):
+    """The Sponza STAND-IN (minipath_b200/scenes.py: atrium_mesh, 263 k triangles) built by the oracle's builder."""
+    from oracle_lib import scenes
+
+    p, n, t = scenes.atrium_mesh()
+    return oracle.build_mesh(p, t, n)
+
+
+@pytest.fixture(scope="session")
+def atrium_camera(atrium):
+    from minipath_b200 import scenes
+
+    return scenes.atrium_camera(*atrium.get_bounding_box())
 
 
 @pytest.fixture(scope="session")

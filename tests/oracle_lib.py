@@ -1,13 +1,33 @@
 """ctypes binding of oracle/liboracle.so — the CPU restatement used ONLY as the checker (tests, smoke, cpu_baseline)."""
 import ctypes as C
+import importlib.util
 import os
+import sys
 
 import numpy as np
 
-from minipath_b200 import HIT_DTYPE, RAY_DTYPE, TILE_DTYPE, _ffi
-
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_PATH = os.path.join(ROOT, "oracle", "liboracle.so")
+
+
+def _load_by_path(name, path):
+    """Import one file of the product package WITHOUT importing the package (whose __init__ maps libminipath_b200.so): the CPU arms
+    of bench.py and the oracle-only tests must be able to run with the checker alone."""
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+# struct mirrors of include/minipath_b200.h (plain ctypes, no library) and the procedural meshes (plain numpy)
+# (registered under its canonical name: if the product package is imported later in the same process it reuses THESE classes, so a
+# BVH built by the oracle can be handed to the product's entry points without a ctypes type mismatch)
+_ffi = _load_by_path("minipath_b200._abi_types", os.path.join(ROOT, "minipath_b200", "_abi_types.py"))
+scenes = sys.modules.get("minipath_b200.scenes") or _load_by_path("_mp_scenes", os.path.join(ROOT, "minipath_b200", "scenes.py"))
+HIT_DTYPE, RAY_DTYPE, TILE_DTYPE = _ffi.HIT_DTYPE, _ffi.RAY_DTYPE, _ffi.TILE_DTYPE
 
 
 class OrcHitRecord(C.Structure):
@@ -52,6 +72,13 @@ def load():
         "orc_render_tiles": (C.c_double, [P(_ffi.MpFlatBvh), P(_ffi.MpCameraSampler), u32, u32, P(_ffi.MpTile), u32, P(_ffi.MpRenderParams), vp,
                                          P(_ffi.MpCounters), i]),
         "orc_resolve_rgba8": (None, [vp, u32, u32, u32, vp]),
+        "orc_bvh_build_obj": (i, [C.c_char_p, i, P(P(_ffi.MpFlatBvh))]),
+        "orc_bvh_build_mesh": (i, [vp, vp, u32, vp, u64, P(P(_ffi.MpFlatBvh))]),
+        "orc_bvh_free": (None, [P(_ffi.MpFlatBvh)]),
+        "orc_build_error": (C.c_char_p, []),
+        "orc_brute_force": (None, [P(_ffi.MpFlatBvh), vp, u64, vp, i]),
+        "orc_camera_sampler": (None, [P(f), P(f), P(f), f, i, f, f, f, u32, u32, P(_ffi.MpCameraSampler)]),
+        "orc_tiles": (u32, [u32, u32, u32, vp, u32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(o, name)
@@ -59,9 +86,113 @@ def load():
     return o
 
 
+class OracleBvh:
+    """A flat BVH made by the ORACLE's own loader and builder (oracle/oracle_build.inc) — a scene source that is not the code under
+    test.  Duck-types minipath_b200.TriangleBvh where the tests need it (``_ptr``, ``raw``, array views, bounding box)."""
+
+    def __init__(self, o, ptr):
+        self._o, self._ptr = o, ptr
+
+    def __del__(self):
+        if getattr(self, "_ptr", None):
+            self._o.orc_bvh_free(self._ptr)
+            self._ptr = None
+
+    @property
+    def raw(self):
+        return self._ptr.contents
+
+    def get_bounding_box(self):
+        r = self.raw
+        return np.array(list(r.bbox_min), np.float32), np.array(list(r.bbox_max), np.float32)
+
+    def _view(self, field, count, dtype, shape):
+        if count == 0:
+            return np.zeros((0,) + shape, dtype)
+        addr = C.cast(getattr(self.raw, field), C.c_void_p).value
+        buf = (C.c_char * (count * int(np.prod(shape)) * np.dtype(dtype).itemsize)).from_address(addr)
+        return np.frombuffer(buf, dtype=dtype).reshape((count,) + shape)
+
+    def inner_bounds(self):
+        return self._view("inner", self.raw.n_inner, np.uint16, (64,))[:, :48].reshape(-1, 6, 8)
+
+    def inner_links(self):
+        return self._view("inner", self.raw.n_inner, np.uint32, (32,))[:, 24:]
+
+    def inner_boxes(self):
+        return self._view("inner_box", self.raw.n_inner, np.float32, (8,))
+
+    def packets(self):
+        return self._view("packets", self.raw.n_packets, np.uint16, (3, 3, 8))
+
+    def packet_boxes(self):
+        return self._view("packet_box", self.raw.n_packets, np.float32, (8,))
+
+    def tri_shading(self):
+        return self._view("tri_shading", self.raw.n_packets * 8, np.uint32, (4,))
+
+    def vertices(self):
+        return self._view("vertices", self.raw.n_vertices, np.float32, (8,))
+
+    def stats(self):
+        """Structural numbers of the tree, walked here in Python (the product's mp_bvh_stats is not used on this side)."""
+        links, n_inner = self.inner_links(), self.raw.n_inner
+        out = {"n_inner": int(n_inner), "n_packets": int(self.raw.n_packets), "n_triangles": int(self.raw.n_triangles), "n_leaves": 0, "max_depth": 0, "max_stack": 1}
+        stack = [(int(self.raw.root), 1, 1)]  # link, depth, stack entries alive when it is popped
+        while stack:
+            link, depth, live = stack.pop()
+            if link == _ffi.LINK_NULL:
+                continue
+            out["max_depth"] = max(out["max_depth"], depth)
+            if link & 7:
+                out["n_leaves"] += 1
+                continue
+            kids = [int(k) for k in links[link >> 3] if int(k) != _ffi.LINK_NULL]
+            out["max_stack"] = max(out["max_stack"], live - 1 + len(kids))
+            for j, k in enumerate(kids):  # child j is popped when j of its siblings are still below it
+                stack.append((k, depth + 1, live - 1 + j + 1))
+        return out
+
+
 class Oracle:
     def __init__(self):
         self.o = load()
+
+    # ---- scene sources that do not touch the product ----
+    def build_obj(self, path, quad_mode=0):
+        out = C.POINTER(_ffi.MpFlatBvh)()
+        if self.o.orc_bvh_build_obj(str(path).encode(), quad_mode, C.byref(out)) != 0:
+            raise RuntimeError("oracle builder: " + self.o.orc_build_error().decode())
+        return OracleBvh(self.o, out)
+
+    def build_mesh(self, positions, triangles, normals=None):
+        pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+        tri = np.ascontiguousarray(triangles, np.uint32).reshape(-1, 3)
+        nrm = None if normals is None else np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+        out = C.POINTER(_ffi.MpFlatBvh)()
+        if self.o.orc_bvh_build_mesh(pos.ctypes.data, None if nrm is None else nrm.ctypes.data, len(pos), tri.ctypes.data, len(tri), C.byref(out)) != 0:
+            raise RuntimeError("oracle builder: " + self.o.orc_build_error().decode())
+        return OracleBvh(self.o, out)
+
+    def brute_force(self, bvh, rays, threads=8):
+        rays = np.ascontiguousarray(rays, RAY_DTYPE)
+        hits = np.empty(len(rays), HIT_DTYPE)
+        self.o.orc_brute_force(bvh._ptr, rays.ctypes.data, len(rays), hits.ctypes.data, threads)
+        return hits
+
+    def camera_sampler(self, center, target, up, resolution, sensor_size=0.024, sensor_is_width=False, focal_length=0.05, f_number=9.0, focus_distance=float("inf")):
+        """Camera::default().look_at(...).build_sampler(resolution) on the oracle side (camera.rs:41-52,93-146)."""
+        f3 = lambda v: (C.c_float * 3)(*[float(x) for x in v])  # noqa: E731
+        s = _ffi.MpCameraSampler()
+        self.o.orc_camera_sampler(f3(center), f3(target), f3(up), sensor_size, int(sensor_is_width), focal_length, f_number, focus_distance,
+                                  int(resolution[0]), int(resolution[1]), C.byref(s))
+        return s
+
+    def tiles(self, width, height, tile_size):
+        n = self.o.orc_tiles(width, height, tile_size, None, 0)
+        arr = np.zeros(n, TILE_DTYPE)
+        self.o.orc_tiles(width, height, tile_size, arr.ctypes.data, n)
+        return arr
 
     def ray_new(self, origin, direction):
         r = _ffi.MpRay()

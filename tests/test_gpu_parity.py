@@ -214,12 +214,12 @@ def test_full_size_properties(gpu_ctx, teapot, teapot_camera):
     assert a[:50].sum() == 0 and a[-50:].sum() == 0  # top/bottom rows are background
 
 
-def test_atrium_standin_bit_exact(gpu_ctx, oracle):
+def test_atrium_standin_bit_exact(gpu_ctx, oracle, atrium, atrium_camera):
     """Sponza STAND-IN (263 k triangles, reference split: depth 16, 106-entry stack): primary rays from its camera plus
     incoherent rays, hits bit-exact; a small 5-bounce wavefront film bit-exact."""
     from minipath_b200 import scenes
 
-    bvh, cam = scenes.atrium_scene()
+    bvh, cam = atrium, atrium_camera
     w, h = 192, 108
     s = _setup(gpu_ctx, bvh, cam, w, h)
     st = mp.RenderSettings(64, 2, (w, h), seed=321, max_bounces=5, mode=mp.MODE_WAVEFRONT)
