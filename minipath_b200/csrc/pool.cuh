@@ -49,6 +49,9 @@ namespace mpd {
 #ifndef POOL_PUSH_RANK
 #define POOL_PUSH_RANK 1 // hit children go to the stack as predicated stores at sp + rank, the top one stays in registers (no per-child branches)
 #endif
+#ifndef POOL_STACK_CG
+#define POOL_STACK_CG 0 // 1: the global stack columns bypass L1 (ld.global.cg / st.global.cg) so that they do not evict node records from it
+#endif
 #ifndef POOL_POP2
 #define POOL_POP2 1     // pop loads two stack entries per iteration (both in flight before either is tested); 0: one
 #endif
@@ -85,17 +88,22 @@ struct PStack {
     uint2* ring;   // shared memory, this ray's column
     uint2* spill;  // global scratch, this ray's column
     int sp, lo;
-    __device__ __forceinline__ uint2& at(int i) const { return spill[(size_t)i * POOL_W]; }  // !SHORT only
+    __device__ __forceinline__ uint2& at(int i) const { return spill[(size_t)i * POOL_W]; }  // !SHORT only (StackSink's lvalue use)
+    __device__ __forceinline__ uint2 ld(int i) const { return POOL_STACK_CG ? __ldcg(spill + (size_t)i * POOL_W) : spill[(size_t)i * POOL_W]; }
+    __device__ __forceinline__ void put(int i, uint2 e) const {
+        if (POOL_STACK_CG) __stcg(spill + (size_t)i * POOL_W, e);
+        else spill[(size_t)i * POOL_W] = e;
+    }
     __device__ __forceinline__ void push(uint2 e) {
         if (SHORT) {
             if (sp - lo == POOL_SS) {  // ring full: the oldest entry goes to the scratch
-                spill[(size_t)lo * POOL_W] = ring[(lo & (POOL_SS - 1)) * POOL_W];
+                put(lo, ring[(lo & (POOL_SS - 1)) * POOL_W]);
                 ++lo;
             }
             ring[(sp & (POOL_SS - 1)) * POOL_W] = e;
             ++sp;
         } else {
-            spill[(size_t)sp * POOL_W] = e;
+            put(sp, e);
             ++sp;
         }
     }
@@ -105,7 +113,7 @@ struct PStack {
             if (sp >= lo) return ring[(sp & (POOL_SS - 1)) * POOL_W];
             lo = sp;  // ring empty: take the entry back from the scratch
         }
-        return spill[(size_t)sp * POOL_W];
+        return ld(sp);
     }
     __device__ __forceinline__ void clear() { sp = 0, lo = 0; }
     __device__ __forceinline__ uint32_t pack() const { return SHORT ? ((uint32_t)sp | (uint32_t)lo << 16) : (uint32_t)sp; }
@@ -160,8 +168,8 @@ __device__ __forceinline__ uint32_t pool_next(const PoolWarp& pw, uint32_t slot,
             // Two entries per iteration, both loads in flight before either is tested: a run of culled entries is otherwise a
             // chain of dependent L2 round trips (13 % of the kernel's stall samples sat on this test, profiles/r1d_wf_pool_32Mpaths.txt).
             const int i = stk.sp - 1;
-            const uint2 a = stk.at(i);
-            const uint2 b = stk.at(i > 0 ? i - 1 : 0);
+            const uint2 a = stk.ld(i);
+            const uint2 b = stk.ld(i > 0 ? i - 1 : 0);
             stk.sp = i;
             if (!(__uint_as_float(a.y) > best_t)) {  // ray_bvh_intersection.rs:40
                 e = a;
@@ -327,14 +335,12 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
                     else
                         mask = inner_quantised_hits<false>(sc, r, node, bt, links, t1s);
                     has_top = mask != 0u;
-                    uint2* dst = stk.spill + (size_t)stk.sp * POOL_W;
 #pragma unroll
                     for (int lane = 0; lane < 8; ++lane) {
                         const bool h = (mask >> lane) & 1u;
                         const bool push = lane < 7 && h && (mask >> (lane + 1)) != 0u;  // a higher lane hit too: this one is not the top
                         if (push) {
-                            *dst = make_uint2(links[lane], __float_as_uint(t1s[lane]));
-                            dst += POOL_W;
+                            stk.put(stk.sp, make_uint2(links[lane], __float_as_uint(t1s[lane])));
                             ++stk.sp;
                         }
                         if (h) top = make_uint2(links[lane], __float_as_uint(t1s[lane]));

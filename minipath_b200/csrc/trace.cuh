@@ -113,11 +113,29 @@ __device__ __forceinline__ bool tri_lane(const uint4 (&q)[9], int lane, const F3
 // 256-bit read-only load (LDG.E.256, sm_100+): a divergent gather costs one L1 wavefront per lane and INSTRUCTION whatever its
 // width (profiles/r1b_ubench_l1_patterns.txt: 10 x LDG.128 = 9.3 clk per node and SM, 5 x LDG.256 = 4.9), so the quantised
 // records are read 32 bytes at a time.
-__device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) {
-    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
-        : "l"(p));
+// MPD_LD_NODE / MPD_LD_PACKET pick the L1 eviction policy of the record loads (0 default, 1 evict_last, 2 no_allocate,
+// 3 evict_first): an A/B switch for scripts/build_variant.sh, measured in profiles/r2c_variants_cache_policy.txt.
+#ifndef MPD_LD_NODE
+#define MPD_LD_NODE 0
+#endif
+#ifndef MPD_LD_PACKET
+#define MPD_LD_PACKET 0
+#endif
+template <int POL>
+__device__ __forceinline__ void ldg256p(const uint4* p, uint4& a, uint4& b) {
+#define MPD_LDG256(Q)                                                                                   \
+    asm("ld.global.nc" Q ".v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"                                     \
+        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)        \
+        : "l"(p))
+    if (POL == 1) MPD_LDG256(".L1::evict_last");
+    else if (POL == 2) MPD_LDG256(".L1::no_allocate");
+    else if (POL == 3) MPD_LDG256(".L1::evict_first");
+    else MPD_LDG256("");
+#undef MPD_LDG256
 }
+__device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) { ldg256p<0>(p, a, b); }
+__device__ __forceinline__ void ldg256n(const uint4* p, uint4& a, uint4& b) { ldg256p<MPD_LD_NODE>(p, a, b); }
+__device__ __forceinline__ void ldg256k(const uint4* p, uint4& a, uint4& b) { ldg256p<MPD_LD_PACKET>(p, a, b); }
 __device__ __forceinline__ float4 as_f4(const uint4& v) { return make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w)); }
 
 // A ray whose inverse direction is finite and non-NaN crosses the planes of a child box in a known order: (b - o) * inv is
@@ -196,11 +214,11 @@ template <bool NANPATH>
 __device__ __forceinline__ uint32_t inner_quantised_hits(const Scene& sc, const Ray& r, uint32_t index, float max_t, uint32_t (&links)[8], float (&t1s)[8]) {
     const uint4* n = sc.inner_rec + 10 * (size_t)index;
     uint4 q[6], la, lb, b0, b1;
-    ldg256(n + 0, q[0], q[1]);
-    ldg256(n + 2, q[2], q[3]);
-    ldg256(n + 4, q[4], q[5]);
-    ldg256(n + 6, la, lb);
-    ldg256(n + 8, b0, b1);
+    ldg256n(n + 0, q[0], q[1]);
+    ldg256n(n + 2, q[2], q[3]);
+    ldg256n(n + 4, q[4], q[5]);
+    ldg256n(n + 6, la, lb);
+    ldg256n(n + 8, b0, b1);
     const F3 bmin = f3(__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b0.z));
     const F3 bsize = f3(__uint_as_float(b1.x), __uint_as_float(b1.y), __uint_as_float(b1.z));
     links[0] = la.x, links[1] = la.y, links[2] = la.z, links[3] = la.w, links[4] = lb.x, links[5] = lb.y, links[6] = lb.z, links[7] = lb.w;
@@ -247,11 +265,11 @@ __device__ __forceinline__ void inner_quantised(const Scene& sc, const Ray& r, u
 #else
     const uint4* n = sc.inner_rec + 10 * (size_t)index;
     uint4 q[6], la, lb, b0, b1;
-    ldg256(n + 0, q[0], q[1]);
-    ldg256(n + 2, q[2], q[3]);
-    ldg256(n + 4, q[4], q[5]);
-    ldg256(n + 6, la, lb);
-    ldg256(n + 8, b0, b1);
+    ldg256n(n + 0, q[0], q[1]);
+    ldg256n(n + 2, q[2], q[3]);
+    ldg256n(n + 4, q[4], q[5]);
+    ldg256n(n + 6, la, lb);
+    ldg256n(n + 8, b0, b1);
     const F3 bmin = f3(__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b0.z));
     const F3 bsize = f3(__uint_as_float(b1.x), __uint_as_float(b1.y), __uint_as_float(b1.z));
     const uint32_t links[8] = {la.x, la.y, la.z, la.w, lb.x, lb.y, lb.z, lb.w};
@@ -268,12 +286,12 @@ __device__ __forceinline__ void inner_quantised(const Scene& sc, const Ray& r, u
 __device__ __forceinline__ void packet_quantised(const Scene& sc, const Ray& r, uint32_t pidx, float max_t, Hit& local) {
     const uint4* pk = sc.packets_rec + 12 * (size_t)pidx;
     uint4 q[9], b0, b1, pad;
-    ldg256(pk + 0, q[0], q[1]);
-    ldg256(pk + 2, q[2], q[3]);
-    ldg256(pk + 4, q[4], q[5]);
-    ldg256(pk + 6, q[6], q[7]);
-    ldg256(pk + 8, q[8], b0);
-    ldg256(pk + 10, b1, pad);
+    ldg256k(pk + 0, q[0], q[1]);
+    ldg256k(pk + 2, q[2], q[3]);
+    ldg256k(pk + 4, q[4], q[5]);
+    ldg256k(pk + 6, q[6], q[7]);
+    ldg256k(pk + 8, q[8], b0);
+    ldg256k(pk + 10, b1, pad);
     const F3 bmin = f3(__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b0.z));
     const F3 bsize = f3(__uint_as_float(b1.x), __uint_as_float(b1.y), __uint_as_float(b1.z));
 #pragma unroll
@@ -355,13 +373,13 @@ __device__ __forceinline__ void inner_decoded(const Scene& sc, const Ray& r, con
 __device__ __forceinline__ uint32_t inner_decoded256_hits(const Scene& sc, const Ray& r, const RaySel& sel, uint32_t index, float max_t, uint32_t (&links)[8], float (&t1s)[8]) {
     const uint4* n = reinterpret_cast<const uint4*>(sc.inner_w + MPD_NODE_W * (size_t)index);
     uint4 ax[2], ay[2], az[2], bx[2], by[2], bz[2], lk[2];
-    ldg256(n + sel.nx, ax[0], ax[1]);
-    ldg256(n + sel.ny, ay[0], ay[1]);
-    ldg256(n + sel.nz, az[0], az[1]);
-    ldg256(n + sel.fx, bx[0], bx[1]);
-    ldg256(n + sel.fy, by[0], by[1]);
-    ldg256(n + sel.fz, bz[0], bz[1]);
-    ldg256(n + 12, lk[0], lk[1]);
+    ldg256n(n + sel.nx, ax[0], ax[1]);
+    ldg256n(n + sel.ny, ay[0], ay[1]);
+    ldg256n(n + sel.nz, az[0], az[1]);
+    ldg256n(n + sel.fx, bx[0], bx[1]);
+    ldg256n(n + sel.fy, by[0], by[1]);
+    ldg256n(n + sel.fz, bz[0], bz[1]);
+    ldg256n(n + 12, lk[0], lk[1]);
     uint32_t mask = 0u;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
