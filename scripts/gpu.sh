@@ -54,7 +54,7 @@ PY
     python scripts/ncu_shares.py gpurun_out/${tag}_launches.csv | tee gpurun_out/${tag}_shares.txt ;;
   ncu)
     tag=$1; regex=$2; skip=$3; count=$4; shift 4
-    timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"$regex" -s $skip -c $count -f -o gpurun_out/$tag \
+    timeout 1200 ncu --set full --clock-control none --import-source on --kernel-name-base ${NCU_BASE:-function} -k regex:"$regex" -s $skip -c $count -f -o gpurun_out/$tag \
         python bench.py --no-cpu-baseline --no-e2e --no-extra --steps 1 --warmup 0 "$@" > gpurun_out/${tag}_ncu.log 2>&1
     python scripts/ncu_summary.py gpurun_out/$tag.ncu-rep | tee gpurun_out/${tag}_summary.txt ;;
   traffic)

@@ -19,6 +19,9 @@ def main(path):
         if w in hdr:
             i = hdr.index(w); print(f'{w} [{units[i]}]', [r[i] for r in rows[2:]])
     for i,h in enumerate(hdr):
+        if h not in WANT and (h.startswith('l1tex__data_pipe_lsu_wavefronts') or h.startswith('l1tex__t_sectors_pipe_lsu_mem_global_op') or h.startswith('l1tex__t_requests_pipe_lsu_mem_global_op')):
+            print(f'{h} [{units[i]}]', [r[i] for r in rows[2:]])
+    for i,h in enumerate(hdr):
         if 'warp_issue_stalled' in h and h.endswith('_per_warp_active.pct'):
             vals=[float(r[i]) for r in rows[2:]]
             if max(vals) > 5: print(h.replace('smsp__warp_issue_stalled_','stall:').replace('_per_warp_active.pct',''), [round(v,1) for v in vals])
