@@ -56,6 +56,7 @@ WORKLOADS = {
     "cube-1080p": ("cube", 1920, 1080, 64, 5),         # configs[1], the cube half
     "teapot-bench": ("teapot", 2048, 1536, 10, 0),     # configs[0]: benches/render_teapot.rs:12-24 (reference shader)
     "atrium-4k": ("atrium", 3840, 2160, 1024, 8),      # configs[3] on the stand-in: spp split over the GPUs, NCCL film reduce
+    "atrium-1080p-materials": ("atrium+materials", 1920, 1080, 256, 5),  # the same frame with the nine per-part materials (RGB path state)
 }
 DEFAULT_WORKLOAD = "atrium-1080p"
 PIPELINES = ["megakernel", "wavefront-octet", "wavefront-thread", "wavefront-persist", "wavefront-hybrid", "wavefront-pool",
@@ -144,14 +145,14 @@ def load_workload(name, args):
     else:
         from minipath_b200 import scenes
 
-        bvh, cam = scenes.atrium_scene()
+        bvh, cam = scenes.atrium_scene(materials=scene.endswith("+materials"))
     return bvh, cam, w, h, spp, bounces
 
 
 def workload_config(name, args):
     """The `config` object both arms print: identical keys and values for the CUDA arm and the reference arm."""
     scene, w, h, spp, bounces = workload_params(name, args)
-    return {"workload": name, "scene": scene + (" (procedural Sponza STAND-IN; sponza.obj is absent from the reference)" if scene == "atrium" else ".obj of the reference"),
+    return {"workload": name, "scene": scene + (" (procedural Sponza STAND-IN; sponza.obj is absent from the reference)" if scene.startswith("atrium") else ".obj of the reference"),
             "resolution": [w, h], "spp": spp, "max_bounces": bounces, "tile_size": 64,
             "l2": "flushed between timed steps (256 MB fill outside the event pairs); inputs resident in HBM",
             "note": "max_bounces>0 is the extension integrator (the reference traces primary rays only)"}
@@ -187,8 +188,15 @@ def oracle_workload(oracle, name, args):
         bvh = oracle.build_obj(os.path.join(data, "cube.obj"), quad_mode=1)
         sampler = oracle.camera_sampler((1.5, 1.2, 2.5), (0, 0, 0), (0, 1, 0), (w, h), f_number=64.0, focus_distance=float(np.linalg.norm([1.5, 1.2, 2.5])))
     else:
-        p, n, t = scenes.atrium_mesh()
-        bvh = oracle.build_mesh(p, t, n)
+        if scene.endswith("+materials"):
+            from oracle_lib import materials_table
+
+            p, n, t, uv, tm, table = scenes.atrium_mesh_materials()
+            bvh = oracle.build_mesh(p, t, n, texcoords=uv, tri_material=tm,
+                                    materials=materials_table(table[:, :3], table[:, 3] > 0, np.where(table[:, 3] > 0, table[:, 3], 1.0)))
+        else:
+            p, n, t = scenes.atrium_mesh()
+            bvh = oracle.build_mesh(p, t, n)
         c = scenes.atrium_camera_params(*bvh.get_bounding_box())
         sampler = oracle.camera_sampler(c["eye"], c["target"], c["up"], (w, h), sensor_size=c["sensor_width"], sensor_is_width=True,
                                         focal_length=c["focal_length"], f_number=c["f_number"], focus_distance=c["focus"])

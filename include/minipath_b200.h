@@ -85,6 +85,22 @@ typedef struct MpVertexShading {
     float _pad1;
 } MpVertexShading;
 
+/* Material table entry (extension).  The reference carries `material: usize` through TriangleShadingData and
+ * HitRecord (mod.rs:40-45; geometry/mod.rs:70-80) but always writes 0 (building.rs:201) and never reads it; here the id is
+ * the low 31 bits of MpTriShading.flags_material and indexes this table.  albedo = Kd of the .mtl entry; MP_MAT_CHECKER
+ * halves it on the odd cells of a grid of `checker_scale` cells per unit of the interpolated texture coordinate
+ * (triangle.rs:229-244) — a procedural stand-in for map_Kd, whose image files the reference's data/ does not ship. */
+typedef struct MpMaterial {
+    float albedo[3];
+    uint32_t flags; /* MP_MAT_* */
+    float checker_scale;
+    float _pad[3];
+} MpMaterial; /* 32 B */
+#define MP_MAT_CHECKER 1u
+#define MP_TRI_MATERIAL_MASK 0x7fffffffu
+#define MP_DEFAULT_ALBEDO 0.7f        /* the grey of scenes without a table, and of .mtl entries without Kd */
+#define MP_DEFAULT_CHECKER_SCALE 4.0f /* cells per texture-coordinate unit given to .mtl entries that have a map_Kd */
+
 typedef struct MpFlatBvh {
     float bbox_min[3];
     float bbox_max[3];
@@ -93,13 +109,14 @@ typedef struct MpFlatBvh {
     uint32_t n_packets;
     uint32_t n_vertices;
     uint32_t n_triangles; /* real (unpadded) triangles */
-    uint32_t _pad;
+    uint32_t n_materials; /* 0 = no table: the extension integrator uses its constant grey albedo for every triangle */
     const MpInnerNode* inner;          /* [n_inner] */
     const MpBox* inner_box;            /* [n_inner]   enclosing box each inner node is decoded against */
     const MpTrianglePacket* packets;   /* [n_packets] */
     const MpBox* packet_box;           /* [n_packets] enclosing box of the leaf the packet belongs to */
     const MpTriShading* tri_shading;   /* [n_packets*8] indexed by packet*8+lane */
     const MpVertexShading* vertices;   /* [n_vertices] */
+    const MpMaterial* materials;       /* [n_materials] or NULL */
 } MpFlatBvh;
 
 /* Host-side scene loading — replaces TriangleBvh::with_obj / build (building.rs:28-120).
@@ -114,6 +131,13 @@ int mp_bvh_build_mesh(const float* positions, const float* normals, uint32_t n_v
  *          1 = median-split builder emitting the same node format (for large soups; not reference-pinned) */
 int mp_bvh_build_mesh_ex(const float* positions, const float* normals, uint32_t n_vertices,
                          const uint32_t* triangles, uint64_t n_triangles, int builder, MpFlatBvh** out);
+/* Same with per-vertex texture coordinates (uv pairs, may be NULL → 0), a material id per triangle (may be NULL → 0) and the
+ * material table (n_materials = 0 → none; every id must be < max(n_materials, 1)).  `mp_bvh_build_obj` fills the same fields
+ * from `mtllib` / `usemtl` / `Kd`: entry 0 is the default material (faces before any `usemtl`), then the .mtl entries in file
+ * order; an OBJ without `mtllib` gets no table. */
+int mp_bvh_build_mesh_mat(const float* positions, const float* normals, const float* texcoords, uint32_t n_vertices,
+                          const uint32_t* triangles, const uint32_t* tri_material, uint64_t n_triangles,
+                          const MpMaterial* materials, uint32_t n_materials, int builder, MpFlatBvh** out);
 int mp_bvh_free(MpFlatBvh* bvh);
 /* Structural statistics (node / packet counts, depth) — printing.rs:11-70 analogue, numbers only. */
 typedef struct MpBvhStats {
@@ -172,6 +196,15 @@ typedef struct MpHit { /* LeafHitRecord (ray_bvh_intersection.rs:165-171) withou
     uint32_t tri;  /* packet*8+lane, MP_NO_HIT on miss */
     float t, u, v;
 } MpHit; /* 16 B */
+
+typedef struct MpHitRecord { /* HitRecord (geometry/mod.rs:70-80) */
+    float t;
+    float point[3];
+    float normal[3];
+    uint32_t material;
+    float texture_coords[3];
+    int32_t hit; /* 0 = miss (Option::None), every other field zero */
+} MpHitRecord; /* 48 B */
 
 #define MP_MODE_MEGAKERNEL 0u /* one thread per pixel runs the whole sample loop */
 #define MP_MODE_WAVEFRONT 1u  /* ray-gen → trace → shade → compact → … → film accumulate */
@@ -303,6 +336,9 @@ int mp_film_read_f32(MpCtx* ctx, float* host_out);
 int mp_trace_rays(MpCtx* ctx, const MpRay* host_rays, uint64_t n, uint32_t order, MpHit* host_out);
 /* Device-resident variant (pointers from mp_dev_alloc or any CUDA allocation). Asynchronous. */
 int mp_trace_rays_device(MpCtx* ctx, const MpRay* dev_rays, uint64_t n, uint32_t order, MpHit* dev_out);
+/* Object::intersect including the hit finalisation (ray_bvh_intersection.rs:66-95; triangle.rs:229-244): point, shading
+ * normal, material id and interpolated texture coordinates per ray — the full HitRecord, bit for bit. */
+int mp_intersect_rays(MpCtx* ctx, const MpRay* host_rays, uint64_t n, uint32_t order, MpHitRecord* host_out);
 /* CameraSampler::sample_ray (camera.rs:176-191) for every (pixel, sample) of the tiles, in
  * tile → row-major pixel → sample order; writes n_pixels*sample_count rays to the host. */
 int mp_generate_rays(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, const MpRenderParams* params,

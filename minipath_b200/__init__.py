@@ -265,14 +265,25 @@ class TriangleBvh:
         return cls(out)
 
     @classmethod
-    def from_mesh(cls, positions, triangles, normals=None, builder=0):
+    def from_mesh(cls, positions, triangles, normals=None, builder=0, texcoords=None, tri_material=None, materials=None):
+        """Indexed mesh → BVH.  ``texcoords`` (n_vertices, 2), ``tri_material`` (n_triangles,) ids into ``materials``, a
+        MATERIAL_DTYPE array (see ``make_materials``); without ``materials`` the extension integrator shades a constant grey."""
         pos = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 3)
         tri = np.ascontiguousarray(triangles, dtype=np.uint32).reshape(-1, 3)
         nrm = None if normals is None else np.ascontiguousarray(normals, dtype=np.float32).reshape(-1, 3)
+        tex = None if texcoords is None else np.ascontiguousarray(texcoords, dtype=np.float32).reshape(-1, 2)
+        tm = None if tri_material is None else np.ascontiguousarray(tri_material, dtype=np.uint32).reshape(-1)
+        mats = None if materials is None else np.ascontiguousarray(materials, dtype=_ffi.MATERIAL_DTYPE).reshape(-1)
+        if tex is not None and len(tex) != len(pos):
+            raise ValueError("texcoords must have one uv pair per vertex")
+        if tm is not None and len(tm) != len(tri):
+            raise ValueError("tri_material must have one id per triangle")
         out = C.POINTER(_ffi.MpFlatBvh)()
-        fp = C.POINTER(C.c_float)
-        check(lib.mp_bvh_build_mesh_ex(pos.ctypes.data_as(fp), None if nrm is None else nrm.ctypes.data_as(fp), len(pos),
-                                       tri.ctypes.data_as(C.POINTER(C.c_uint32)), len(tri), builder, C.byref(out)))
+        fp, up = C.POINTER(C.c_float), C.POINTER(C.c_uint32)
+        check(lib.mp_bvh_build_mesh_mat(pos.ctypes.data_as(fp), None if nrm is None else nrm.ctypes.data_as(fp),
+                                        None if tex is None else tex.ctypes.data_as(fp), len(pos), tri.ctypes.data_as(up),
+                                        None if tm is None else tm.ctypes.data_as(up), len(tri),
+                                        None if mats is None else mats.ctypes.data, 0 if mats is None else len(mats), builder, C.byref(out)))
         return cls(out)
 
     def __del__(self):
@@ -322,6 +333,24 @@ class TriangleBvh:
 
     def vertices(self):
         return self._view("vertices", self.raw.n_vertices, np.float32, (8,))
+
+    def materials(self):
+        r = self.raw
+        if r.n_materials == 0:
+            return np.zeros(0, _ffi.MATERIAL_DTYPE)
+        buf = (C.c_char * (r.n_materials * _ffi.MATERIAL_DTYPE.itemsize)).from_address(C.cast(r.materials, C.c_void_p).value)
+        return np.frombuffer(buf, dtype=_ffi.MATERIAL_DTYPE)
+
+
+def make_materials(albedos, checker=None, checker_scale=None):
+    """MATERIAL_DTYPE table from (n, 3) albedos; ``checker`` marks the entries that get the procedural checker."""
+    alb = np.asarray(albedos, np.float32).reshape(-1, 3)
+    m = np.zeros(len(alb), _ffi.MATERIAL_DTYPE)
+    m["albedo"] = alb
+    m["checker_scale"] = _ffi.DEFAULT_CHECKER_SCALE if checker_scale is None else np.asarray(checker_scale, np.float32)
+    if checker is not None:
+        m["flags"] = np.where(np.asarray(checker, bool), _ffi.MAT_CHECKER, 0).astype(np.uint32)
+    return m
 
 
 class Scene:
@@ -461,6 +490,7 @@ class Context:
         else:
             self._h = _borrowed  # a group member's context: the group owns it
         self.resolution = None
+        self.trace_variant = TRACE_THREAD  # what mp_ctx_create starts with
 
     def close(self):
         if getattr(self, "_h", None):
@@ -480,6 +510,7 @@ class Context:
 
     def set_trace_variant(self, variant):
         check(lib.mp_ctx_set_trace_variant(self._h, variant))
+        self.trace_variant = variant
 
     def set_node_layout(self, layout):
         """LAYOUT_AUTO (default), LAYOUT_DECODED (f32 child boxes / triangle edges written at upload) or LAYOUT_QUANTISED (reference records)."""
@@ -572,6 +603,13 @@ class Context:
         hits = np.empty(len(rays), dtype=HIT_DTYPE)
         check(lib.mp_trace_rays(self._h, rays.ctypes.data, len(rays), order, hits.ctypes.data))
         return hits
+
+    def intersect_rays(self, rays, order=ORDER_REFERENCE):
+        """Object::intersect with hit finalisation: HitRecord {t, point, normal, material, texture_coords} per ray."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        out = np.empty(len(rays), dtype=_ffi.HIT_RECORD_DTYPE)
+        check(lib.mp_intersect_rays(self._h, rays.ctypes.data, len(rays), order, out.ctypes.data))
+        return out
 
     def trace_rays_device(self, dev_rays, n, dev_hits, order=ORDER_REFERENCE):
         """Object::intersect on rays already resident in HBM (device pointers, e.g. torch tensors); asynchronous."""

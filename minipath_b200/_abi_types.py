@@ -13,6 +13,10 @@ LINK_MAX_INDEX = 0x1FFFFFFE
 LINK_MAX_COUNT = 7
 NO_HIT = 0xFFFFFFFF
 TRI_FLAT = 0x80000000
+TRI_MATERIAL_MASK = 0x7FFFFFFF
+MAT_CHECKER = 1
+DEFAULT_ALBEDO = 0.7
+DEFAULT_CHECKER_SCALE = 4.0
 MODE_MEGAKERNEL, MODE_WAVEFRONT = 0, 1
 ORDER_REFERENCE, ORDER_NEAR_FIRST = 0, 1
 MODE_AUTO = 2
@@ -42,6 +46,10 @@ class MpVertexShading(C.Structure):
     _fields_ = [("normal", C.c_float * 3), ("_pad0", C.c_float), ("tex", C.c_float * 3), ("_pad1", C.c_float)]
 
 
+class MpMaterial(C.Structure):
+    _fields_ = [("albedo", C.c_float * 3), ("flags", C.c_uint32), ("checker_scale", C.c_float), ("_pad", C.c_float * 3)]
+
+
 class MpFlatBvh(C.Structure):
     _fields_ = [
         ("bbox_min", C.c_float * 3),
@@ -51,13 +59,14 @@ class MpFlatBvh(C.Structure):
         ("n_packets", C.c_uint32),
         ("n_vertices", C.c_uint32),
         ("n_triangles", C.c_uint32),
-        ("_pad", C.c_uint32),
+        ("n_materials", C.c_uint32),
         ("inner", C.POINTER(MpInnerNode)),
         ("inner_box", C.POINTER(MpBox)),
         ("packets", C.POINTER(MpTrianglePacket)),
         ("packet_box", C.POINTER(MpBox)),
         ("tri_shading", C.POINTER(MpTriShading)),
         ("vertices", C.POINTER(MpVertexShading)),
+        ("materials", C.POINTER(MpMaterial)),
     ]
 
 
@@ -112,6 +121,17 @@ class MpHit(C.Structure):
     _fields_ = [("tri", C.c_uint32), ("t", C.c_float), ("u", C.c_float), ("v", C.c_float)]
 
 
+class MpHitRecord(C.Structure):
+    _fields_ = [
+        ("t", C.c_float),
+        ("point", C.c_float * 3),
+        ("normal", C.c_float * 3),
+        ("material", C.c_uint32),
+        ("texture_coords", C.c_float * 3),
+        ("hit", C.c_int32),
+    ]
+
+
 class MpRenderParams(C.Structure):
     _fields_ = [
         ("sample_count", C.c_uint32),
@@ -158,4 +178,6 @@ class MpProgressSnapshot(C.Structure):
 
 RAY_DTYPE = np.dtype([("origin", "<f4", 3), ("direction", "<f4", 3), ("inv_direction", "<f4", 3)])
 HIT_DTYPE = np.dtype([("tri", "<u4"), ("t", "<f4"), ("u", "<f4"), ("v", "<f4")])
+HIT_RECORD_DTYPE = np.dtype([("t", "<f4"), ("point", "<f4", 3), ("normal", "<f4", 3), ("material", "<u4"), ("texture_coords", "<f4", 3), ("hit", "<i4")])
+MATERIAL_DTYPE = np.dtype([("albedo", "<f4", 3), ("flags", "<u4"), ("checker_scale", "<f4"), ("_pad", "<f4", 3)])
 TILE_DTYPE = np.dtype([("min_x", "<u4"), ("min_y", "<u4"), ("max_x", "<u4"), ("max_y", "<u4")])

@@ -36,6 +36,7 @@ PROTOTYPES = {
     "mp_bvh_build_obj": (_i, [C.c_char_p, _i, _P(_P(MpFlatBvh))]),
     "mp_bvh_build_mesh": (_i, [_P(C.c_float), _P(C.c_float), _u32, _P(_u32), _u64, _P(_P(MpFlatBvh))]),
     "mp_bvh_build_mesh_ex": (_i, [_P(C.c_float), _P(C.c_float), _u32, _P(_u32), _u64, _i, _P(_P(MpFlatBvh))]),
+    "mp_bvh_build_mesh_mat": (_i, [_P(C.c_float), _P(C.c_float), _P(C.c_float), _u32, _P(_u32), _P(_u32), _u64, _vp, _u32, _i, _P(_P(MpFlatBvh))]),
     "mp_bvh_free": (_i, [_P(MpFlatBvh)]),
     "mp_bvh_stats": (_i, [_P(MpFlatBvh), _P(MpBvhStats)]),
     "mp_camera_default": (_i, [_P(MpCamera)]),
@@ -79,6 +80,7 @@ PROTOTYPES = {
     "mp_film_read_f32": (_i, [_vp, _vp]),
     "mp_trace_rays": (_i, [_vp, _vp, _u64, _u32, _vp]),
     "mp_trace_rays_device": (_i, [_vp, _vp, _u64, _u32, _vp]),
+    "mp_intersect_rays": (_i, [_vp, _vp, _u64, _u32, _vp]),
     "mp_generate_rays": (_i, [_vp, _P(MpTile), _u32, _P(MpRenderParams), _vp, _u64, _P(_u64)]),
     "mp_dev_alloc": (_i, [_vp, C.c_size_t, _P(_vp)]),
     "mp_dev_free": (_i, [_vp, _vp]),

@@ -316,6 +316,13 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     if (!b || !b->packets || !b->packet_box || !b->tri_shading || !b->vertices || (b->n_inner && (!b->inner || !b->inner_box)))
         return fail(MP_EINVAL, "incomplete MpFlatBvh");
     if (b->n_packets == 0) return fail(MP_EINVAL, "scene has no triangle packets");
+    if (b->n_materials && !b->materials) return fail(MP_EINVAL, "n_materials without a table");
+    {  // every real triangle's material id must index the table (the kernels do not clamp)
+        const uint32_t limit = std::max(b->n_materials, 1u);
+        for (size_t i = 0, n = (size_t)b->n_packets * 8; i < n; ++i)
+            if ((b->tri_shading[i].flags_material & MP_TRI_MATERIAL_MASK) >= limit)
+                return fail(MP_EINVAL, "triangle %zu has material %u, the table has %u entries", i, b->tri_shading[i].flags_material & MP_TRI_MATERIAL_MASK, b->n_materials);
+    }
     MpBvhStats st;
     if (int rc = mp_bvh_stats(b, &st)) return rc;
     if (st.max_stack > MPD_OCTET_STACK_MAX) return fail(MP_EINVAL, "BVH depth %u needs a %u-entry stack (limit %d)", st.max_depth, st.max_stack, MPD_OCTET_STACK_MAX);
@@ -327,7 +334,8 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     const size_t s_sh = al((size_t)b->n_packets * 8 * sizeof(MpTriShading)), s_v = al((size_t)b->n_vertices * sizeof(MpVertexShading));
     const size_t s_inner_w = al((size_t)b->n_inner * MPD_NODE_W * sizeof(float4)), s_pack_w = al((size_t)b->n_packets * MPD_PACK_W * sizeof(float4));
     const size_t s_inner_r = al((size_t)b->n_inner * 160), s_pack_r = al((size_t)b->n_packets * 192);
-    const size_t total = 2 * s_inner + s_ibox + 2 * s_pack + s_pbox + s_sh + s_v + s_inner_w + s_pack_w + s_inner_r + s_pack_r + 256;
+    const size_t s_mat = al((size_t)b->n_materials * sizeof(MpMaterial));
+    const size_t total = 2 * s_inner + s_ibox + 2 * s_pack + s_pbox + s_sh + s_v + s_inner_w + s_pack_w + s_inner_r + s_pack_r + s_mat + 256;
     if (total > ctx->scene_blob_cap) {  // pooled contexts keep the allocation between renders
         if (ctx->d_scene_blob) CK(cudaFree(ctx->d_scene_blob));
         ctx->d_scene_blob = nullptr, ctx->scene_blob_cap = 0, ctx->has_scene = false;
@@ -347,6 +355,8 @@ int mp_scene_upload(MpCtx* ctx, const MpFlatBvh* b) {
     ctx->scene.packet_box = (const float4*)up(b->packet_box, (size_t)b->n_packets * sizeof(MpBox), s_pbox);
     ctx->scene.tri_shading = (const uint4*)up(b->tri_shading, (size_t)b->n_packets * 8 * sizeof(MpTriShading), s_sh);
     ctx->scene.vertices = (const float4*)up(b->vertices, (size_t)b->n_vertices * sizeof(MpVertexShading), s_v);
+    ctx->scene.materials = b->n_materials ? (const float4*)up(b->materials, (size_t)b->n_materials * sizeof(MpMaterial), s_mat) : nullptr;
+    ctx->scene.n_materials = b->n_materials;
     // child-major copies for the octet kernels (octet.cuh), written on the device
     uint4* inner_cm = (uint4*)p;
     p += s_inner;

@@ -38,6 +38,7 @@ struct VertexData {  // building.rs:220-224
 };
 struct Tri {
     uint32_t v[3];
+    uint32_t material;  // index into the material table (0 when there is none)
     V3 c;           // centroid and bounds, filled once by build_flat: the builders sort triangles many times and would
     V3 bmin, bmax;  // otherwise gather the three vertices (a cache miss each) at every level
 };
@@ -67,9 +68,42 @@ static bool parse_index_tuple(const std::string& tok, long nv, long nvt, long nv
     return out[0] >= 0;
 }
 
-static int load_obj(const char* path, int quad_mode, std::vector<Tri>& triangles, std::vector<VertexData>& vertices) {
+// `newmtl` / `Kd` / `map_Kd` of a .mtl library, appended to `materials` in file order.  A material with a diffuse map gets the
+// checker flag: the map images are not part of the data set, the interpolated texture coordinate drives a procedural pattern.
+static int load_mtl(const std::string& path, std::vector<MpMaterial>& materials, std::map<std::string, uint32_t>& id_of) {
+    std::ifstream f(path);
+    if (!f) return fail(MP_EIO, "Failed to read file: %s", path.c_str());
+    std::string line;
+    MpMaterial* cur = nullptr;
+    while (std::getline(f, line)) {
+        std::istringstream ss(line);
+        std::string tag;
+        if (!(ss >> tag)) continue;
+        if (tag == "newmtl") {
+            std::string name;
+            ss >> name;
+            MpMaterial m{};
+            m.albedo[0] = m.albedo[1] = m.albedo[2] = MP_DEFAULT_ALBEDO;
+            m.checker_scale = MP_DEFAULT_CHECKER_SCALE;
+            id_of[name] = (uint32_t)materials.size();
+            materials.push_back(m);
+            cur = &materials.back();
+        } else if (tag == "Kd" && cur) {
+            double r = 0, g = 0, b = 0;
+            ss >> r >> g >> b;
+            cur->albedo[0] = (float)r, cur->albedo[1] = (float)g, cur->albedo[2] = (float)b;
+        } else if (tag == "map_Kd" && cur) {
+            cur->flags |= MP_MAT_CHECKER;
+        }
+    }
+    return MP_OK;
+}
+
+static int load_obj(const char* path, int quad_mode, std::vector<Tri>& triangles, std::vector<VertexData>& vertices, std::vector<MpMaterial>& materials) {
     std::ifstream f(path);
     if (!f) return fail(MP_EIO, "Failed to read file: %s", path);
+    std::map<std::string, uint32_t> material_id;
+    uint32_t current_material = 0;
     std::vector<std::array<double, 3>> P, N;
     std::vector<std::array<double, 2>> T;
     std::map<std::tuple<long, long, long>, uint32_t> index_of;  // IndexMap: id = insertion index (building.rs:49-50)
@@ -91,6 +125,24 @@ static int load_obj(const char* path, int quad_mode, std::vector<Tri>& triangles
             std::array<double, 2> p{0, 0};
             ss >> p[0] >> p[1];
             T.push_back(p);
+        } else if (tag == "mtllib") {
+            if (materials.empty()) {  // entry 0: faces that precede every `usemtl`
+                MpMaterial m{};
+                m.albedo[0] = m.albedo[1] = m.albedo[2] = MP_DEFAULT_ALBEDO;
+                m.checker_scale = MP_DEFAULT_CHECKER_SCALE;
+                materials.push_back(m);
+            }
+            std::string name, dir(path);
+            const size_t slash = dir.find_last_of('/');
+            dir = slash == std::string::npos ? std::string() : dir.substr(0, slash + 1);
+            while (ss >> name)
+                if (int rc = load_mtl(name[0] == '/' ? name : dir + name, materials, material_id)) return rc;
+        } else if (tag == "usemtl") {
+            std::string name;
+            ss >> name;
+            auto it = material_id.find(name);
+            if (it == material_id.end()) return fail(MP_EIO, "Failed to parse file: %s: unknown material '%s'", path, name.c_str());
+            current_material = it->second;
         } else if (tag == "f") {
             std::vector<uint32_t> poly;
             std::string tok;
@@ -135,7 +187,7 @@ static int load_obj(const char* path, int quad_mode, std::vector<Tri>& triangles
                 }
                 poly.push_back(id);
             }
-            for (size_t k = 2; k < poly.size(); ++k) triangles.push_back(Tri{{poly[0], poly[k - 1], poly[k]}, V3{}, V3{}, V3{}});
+            for (size_t k = 2; k < poly.size(); ++k) triangles.push_back(Tri{{poly[0], poly[k - 1], poly[k]}, current_material, V3{}, V3{}, V3{}});
         }
     }
     if (skipped) fprintf(stderr, "minipath_b200: %zu non-triangle primitive(s) skipped in %s\n", skipped, path);

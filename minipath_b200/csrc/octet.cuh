@@ -299,7 +299,8 @@ __global__ void __launch_bounds__(128) wf_trace_octet_kernel(Scene sc, SceneCM c
 template <int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) wf_shadow_octet_kernel(Scene sc, SceneCM cm, const float4* __restrict__ sh_o,
                                                               const uint32_t* __restrict__ sh_path, const uint32_t* __restrict__ sh_count,
-                                                              float4* __restrict__ ray_d, DevCounters* dc, uint32_t stack_cap) {
+                                                              float4* __restrict__ ray_d, float4* __restrict__ rgb, const float2* __restrict__ sh_c,
+                                                              DevCounters* dc, uint32_t stack_cap) {
     extern __shared__ uint2 octet_stacks[];
     uint2* stk = octet_stacks + (threadIdx.x >> 3) * stack_cap;
     const OctetLane ol = octet_lane();
@@ -315,10 +316,7 @@ __global__ void __launch_bounds__(128) wf_shadow_octet_kernel(Scene sc, SceneCM 
             tc.shadow_rays++;
         },
         [&](uint32_t i, const Hit& h) {
-            if (ol.sub == 0 && h.tri == MP_NO_HIT) {
-                const uint32_t path = sh_path[i];
-                ray_d[path].w = __fadd_rn(ray_d[path].w, contribution);
-            }
+            if (ol.sub == 0 && h.tri == MP_NO_HIT) add_sun(ray_d, rgb, sh_c, sh_path[i], i, contribution);
         },
         tc);
     octet_finish_counts(dc, tc, COUNT);

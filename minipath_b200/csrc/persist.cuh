@@ -128,7 +128,8 @@ __global__ void __launch_bounds__(128) wf_trace_persist_kernel(Scene sc, const u
 
 template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128) wf_shadow_persist_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
-                                                                const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, DevCounters* dc) {
+                                                                const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, float4* __restrict__ rgb,
+                                                                const float2* __restrict__ sh_c, DevCounters* dc) {
     ThreadCounts tc{};
     float contribution = 0.0f;
     const Ray sun = ray_new(f3(0.f, 0.f, 0.f), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
@@ -141,10 +142,7 @@ __global__ void __launch_bounds__(128) wf_shadow_persist_kernel(Scene sc, const 
             tc.shadow_rays++;
         },
         [&](uint32_t i, const Hit& h) {
-            if (h.tri == MP_NO_HIT) {
-                const uint32_t path = sh_path[i];
-                ray_d[path].w = __fadd_rn(ray_d[path].w, contribution);
-            }
+            if (h.tri == MP_NO_HIT) add_sun(ray_d, rgb, sh_c, sh_path[i], i, contribution);
         },
         tc);
     flush_counts(dc, tc, COUNT);

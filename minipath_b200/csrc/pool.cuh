@@ -595,8 +595,9 @@ __global__ void __launch_bounds__(128, POOL_BLOCKS_FOR(LAYOUT)) wf_trace_pool_ke
 
 template <int LAYOUT, int ORDER, bool COUNT>
 __global__ void __launch_bounds__(128, POOL_BLOCKS_FOR(LAYOUT)) wf_shadow_pool_kernel(Scene sc, const float4* __restrict__ sh_o, const uint32_t* __restrict__ sh_path,
-                                                             const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, DevCounters* dc,
-                                                             uint32_t* claim, uint2* scratch, uint32_t stack_cap) {
+                                                             const uint32_t* __restrict__ sh_count, float4* __restrict__ ray_d, float4* __restrict__ rgb,
+                                                             const float2* __restrict__ sh_c, DevCounters* dc, uint32_t* claim, uint2* scratch,
+                                                             uint32_t stack_cap) {
     extern __shared__ __align__(16) unsigned char pool_smem[];
     ThreadCounts tc{};
     const Ray sun = ray_new(f3(0.f, 0.f, 0.f), f3(EXT_SUN_X, EXT_SUN_Y, EXT_SUN_Z));
@@ -608,10 +609,7 @@ __global__ void __launch_bounds__(128, POOL_BLOCKS_FOR(LAYOUT)) wf_shadow_pool_k
             tc.shadow_rays++;
         },
         [&](uint32_t i, const Hit& h) {
-            if (h.tri == MP_NO_HIT) {
-                const uint32_t path = sh_path[i];
-                ray_d[path].w = __fadd_rn(ray_d[path].w, sh_o[i].w);
-            }
+            if (h.tri == MP_NO_HIT) add_sun(ray_d, rgb, sh_c, sh_path[i], i, sh_o[i].w);
         },
         tc, &sun);
     flush_counts(dc, tc, COUNT);

@@ -31,6 +31,8 @@ struct Scene {
     const float4* __restrict__ packets_w;  // decoded packets, MPD_PACK_W float4 each
     uint32_t root;
     float eps;  // extension integrator: origin offset, 1e-4 * scene diagonal
+    const float4* __restrict__ materials;  // 2 x float4 per MpMaterial, or null (no table: constant grey albedo)
+    uint32_t n_materials;
     uint32_t minmax_ok;  // every real child box has min <= max after dequantisation (checked by decode_inner_kernel at upload)
 };
 

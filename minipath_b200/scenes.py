@@ -28,15 +28,16 @@ def _surface(fn, nu, nv):
     n = np.cross(fn(u + e, v) - fn(u - e, v), fn(u, v + e) - fn(u, v - e))
     ln = np.linalg.norm(n, axis=-1, keepdims=True)
     n = np.where(ln > 0, n / np.maximum(ln, 1e-30), np.array([0.0, 1.0, 0.0]))
-    return p.reshape(-1, 3), n.reshape(-1, 3), _grid(nu, nv)
+    return p.reshape(-1, 3), n.reshape(-1, 3), _grid(nu, nv), np.stack([u, v], -1).reshape(-1, 2)
 
 
 class _Mesh:
     def __init__(self):
-        self.p, self.n, self.t, self.base = [], [], [], 0
+        self.p, self.n, self.t, self.uv, self.m, self.base, self.part = [], [], [], [], [], 0, 0
 
-    def add(self, p, n, t):
-        self.p.append(p), self.n.append(n), self.t.append(t + self.base)
+    def add(self, p, n, t, uv):
+        self.p.append(p), self.n.append(n), self.t.append(t + self.base), self.uv.append(uv)
+        self.m.append(np.full(len(t), self.part, np.uint32))
         self.base += len(p)
 
     def arrays(self):
@@ -44,8 +45,35 @@ class _Mesh:
                 np.concatenate(self.t).astype(np.uint32))
 
 
+# parts of the stand-in, in the order atrium_mesh() emits them: (name, albedo, checker cells per uv unit or 0)
+ATRIUM_PARTS = (
+    ("floor", (0.62, 0.58, 0.52), 24.0),
+    ("walls", (0.78, 0.70, 0.58), 0.0),
+    ("columns", (0.80, 0.78, 0.72), 0.0),
+    ("arches", (0.72, 0.66, 0.60), 0.0),
+    ("gallery", (0.55, 0.50, 0.46), 8.0),
+    ("cloth_red", (0.75, 0.12, 0.10), 0.0),
+    ("cloth_green", (0.14, 0.55, 0.18), 6.0),
+    ("cloth_blue", (0.12, 0.20, 0.70), 0.0),
+    ("vases", (0.30, 0.45, 0.55), 0.0),
+)
+
+
 def atrium_mesh():
     """Returns (positions[nv,3] f32, normals[nv,3] f32, triangles[nt,3] u32)."""
+    return _atrium().arrays()
+
+
+def atrium_mesh_materials():
+    """The same stand-in with per-part materials: (positions, normals, triangles, texcoords[nv,2] f32, tri_material[nt] u32,
+    materials as rows (albedo r, g, b, checker cells per uv unit or 0)) — SURVEY §8 f3."""
+    m = _atrium()
+    p, n, t = m.arrays()
+    table = np.array([[*a, c] for _, a, c in ATRIUM_PARTS], np.float32)
+    return p, n, t, np.concatenate(m.uv).astype(np.float32), np.concatenate(m.m), table
+
+
+def _atrium():
     rng = np.random.Generator(np.random.PCG64(ATRIUM_SEED))
     m = _Mesh()
     L, W, H = 30.0, 12.0, 10.0  # x, z, y extents
@@ -53,8 +81,10 @@ def atrium_mesh():
 
     # floor with slightly uneven flagstones, long and short walls
     bump = rng.uniform(-0.01, 0.01, (65, 161))
+    m.part = 0
     m.add(*_surface(lambda u, v: S([u * L - L / 2, 0.02 * np.sin(40 * u) * np.sin(36 * v) + 0 * u, v * W - W / 2], -1), 160, 64))
     m.p[-1][:, 1] += bump.reshape(-1)
+    m.part = 1
     for z, s in ((-W / 2, 1.0), (W / 2, -1.0)):
         m.add(*_surface(lambda u, v, z=z, s=s: S([(u if s > 0 else 1 - u) * L - L / 2, v * H, z + 0.03 * s * np.sin(25 * u) * np.cos(9 * v)], -1), 160, 48))
     for x, s in ((-L / 2, 1.0), (L / 2, -1.0)):
@@ -66,14 +96,17 @@ def atrium_mesh():
         for z in (-W / 2 + 2.2, W / 2 - 2.2):
             for x in xs:
                 r = 0.32 - 0.04 * level
+                m.part = 2
                 m.add(*_surface(lambda u, v, x=x, z=z, r=r, y0=y0, y1=y1: S([
                     x + r * (1 + 0.06 * np.cos(16 * 2 * np.pi * u)) * (1 - 0.15 * v) * np.cos(2 * np.pi * u), y0 + v * (y1 - y0),
                     z - r * (1 + 0.06 * np.cos(16 * 2 * np.pi * u)) * (1 - 0.15 * v) * np.sin(2 * np.pi * u)], -1), 32, 24))
             for xa, xb in zip(xs[:-1], xs[1:]):
                 cx, R = 0.5 * (xa + xb), 0.5 * (xb - xa)
+                m.part = 3
                 m.add(*_surface(lambda u, v, cx=cx, R=R, z=z, y1=y1: S([
                     cx - (R + 0.18 * np.cos(2 * np.pi * v)) * np.cos(np.pi * u), y1 + 0.45 * (R + 0.18 * np.cos(2 * np.pi * v)) * np.sin(np.pi * u),
                     z + 0.18 * np.sin(2 * np.pi * v)], -1), 16, 24))
+    m.part = 4
     for z0, z1 in ((-W / 2, -W / 2 + 2.6), (W / 2 - 2.6, W / 2)):
         m.add(*_surface(lambda u, v, z0=z0, z1=z1: S([u * L - L / 2, 4.3 + 0 * u, z0 + v * (z1 - z0)], -1), 160, 8))
         m.add(*_surface(lambda u, v, z0=z0, z1=z1: S([(1 - u) * L - L / 2, 4.2 + 0 * u, z0 + v * (z1 - z0)], -1), 160, 8))
@@ -82,17 +115,19 @@ def atrium_mesh():
     for k in range(6):
         x0 = -L / 2 + 3.0 + k * 4.6
         ph = rng.uniform(0, 2 * np.pi, 3)
+        m.part = 5 + k % 3
         m.add(*_surface(lambda u, v, x0=x0, ph=ph: S([
             x0 + 1.6 * u + 0.15 * np.sin(9 * v + ph[0]), 8.6 - 3.2 * v - 0.9 * np.sin(np.pi * u) * (0.3 + v) + 0.08 * np.sin(14 * u + ph[1]),
             -2.4 + 4.8 * u * 0 + 2.4 * np.sin(np.pi * (u - 0.5)) + 0.2 * np.sin(11 * v + ph[2])], -1), 64, 64))
 
     # vases on the floor
+    m.part = 8
     for k in range(16):
         cx, cz = -L / 2 + 1.5 + (k % 8) * 3.85, (-1.0 if k < 8 else 1.0) * 1.4
         m.add(*_surface(lambda u, v, cx=cx, cz=cz: S([
             cx + (0.25 + 0.22 * np.sin(np.pi * v) ** 2) * np.cos(2 * np.pi * u), 0.05 + 1.1 * v,
             cz - (0.25 + 0.22 * np.sin(np.pi * v) ** 2) * np.sin(2 * np.pi * u)], -1), 32, 32))
-    return m.arrays()
+    return m
 
 
 def atrium_camera_params(bbox_min, bbox_max):
@@ -119,15 +154,22 @@ def atrium_camera(bbox_min, bbox_max):
 _ATRIUM_CACHE = {}
 
 
-def atrium_scene(builder=0):
-    """(TriangleBvh, Camera) of the Sponza stand-in; the BVH uses the reference split unless builder=1."""
-    from . import TriangleBvh
+def atrium_scene(builder=0, materials=False):
+    """(TriangleBvh, Camera) of the Sponza stand-in; the BVH uses the reference split unless builder=1.  ``materials``: with the
+    per-part material table (same geometry, same tree)."""
+    from . import TriangleBvh, make_materials
 
-    if builder not in _ATRIUM_CACHE:
-        p, n, t = atrium_mesh()
-        bvh = TriangleBvh.from_mesh(p, t, normals=n, builder=builder)
-        _ATRIUM_CACHE[builder] = (bvh, atrium_camera(*bvh.get_bounding_box()))
-    return _ATRIUM_CACHE[builder]
+    key = (builder, bool(materials))
+    if key not in _ATRIUM_CACHE:
+        if materials:
+            p, n, t, uv, tm, table = atrium_mesh_materials()
+            mats = make_materials(table[:, :3], checker=table[:, 3] > 0, checker_scale=np.where(table[:, 3] > 0, table[:, 3], 1.0))
+            bvh = TriangleBvh.from_mesh(p, t, normals=n, builder=builder, texcoords=uv, tri_material=tm, materials=mats)
+        else:
+            p, n, t = atrium_mesh()
+            bvh = TriangleBvh.from_mesh(p, t, normals=n, builder=builder)
+        _ATRIUM_CACHE[key] = (bvh, atrium_camera(*bvh.get_bounding_box()))
+    return _ATRIUM_CACHE[key]
 
 
 def soup_mesh(n_triangles, seed=None):

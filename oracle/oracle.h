@@ -80,6 +80,7 @@ typedef struct OrcHitRecord { /* geometry/mod.rs:71-80 */
 } OrcHitRecord;
 /* Object::intersect including finalisation (ray_bvh_intersection.rs:66-95) */
 void orc_intersect(const MpFlatBvh* bvh, const MpRay* ray, uint32_t order, OrcHitRecord* out);
+void orc_intersect_rays(const MpFlatBvh* bvh, const MpRay* rays, uint64_t n, uint32_t order, OrcHitRecord* out, int threads);
 
 /* CameraSampler::sample_ray (camera.rs:176-191) with the shared RNG */
 void orc_sample_ray(const MpCameraSampler* cam, uint32_t px, uint32_t py, uint32_t* rng_state, MpRay* out);
@@ -100,6 +101,9 @@ void orc_resolve_rgba8(const float* film, uint32_t width, uint32_t height, uint3
  * Returns 0, or -1 with orc_build_error() where the reference would panic.  The arrays carry the box tables too, so the same
  * MpFlatBvh can be uploaded to the GPU: the device then traverses a tree the product did not build. */
 int orc_bvh_build_obj(const char* path, int quad_mode, MpFlatBvh** out);
+/* with texture coordinates (uv pairs or NULL), a material id per triangle (or NULL) and the material table */
+int orc_bvh_build_mesh_mat(const float* positions, const float* normals, const float* texcoords, uint32_t n_vertices, const uint32_t* triangles,
+                           const uint32_t* tri_material, uint64_t n_triangles, const MpMaterial* materials, uint32_t n_materials, MpFlatBvh** out);
 int orc_bvh_build_mesh(const float* positions, const float* normals, uint32_t n_vertices, const uint32_t* triangles,
                        uint64_t n_triangles, MpFlatBvh** out);
 void orc_bvh_free(MpFlatBvh* bvh);

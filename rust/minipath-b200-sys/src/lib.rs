@@ -85,6 +85,20 @@ pub struct MpVertexShading {
     pub _pad1: f32,
 }
 
+/// Material table entry (extension): albedo = Kd, MP_MAT_CHECKER halves it on the odd cells of the texture-coordinate grid.
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct MpMaterial {
+    pub albedo: [f32; 3],
+    pub flags: u32,
+    pub checker_scale: f32,
+    pub _pad: [f32; 3],
+}
+pub const MP_MAT_CHECKER: u32 = 1;
+pub const MP_TRI_MATERIAL_MASK: u32 = 0x7fff_ffff;
+pub const MP_DEFAULT_ALBEDO: f32 = 0.7;
+pub const MP_DEFAULT_CHECKER_SCALE: f32 = 4.0;
+
 #[repr(C)]
 #[derive(Clone, Copy, Debug)]
 pub struct MpFlatBvh {
@@ -95,13 +109,14 @@ pub struct MpFlatBvh {
     pub n_packets: u32,
     pub n_vertices: u32,
     pub n_triangles: u32,
-    pub _pad: u32,
+    pub n_materials: u32,
     pub inner: *const MpInnerNode,
     pub inner_box: *const MpBox,
     pub packets: *const MpTrianglePacket,
     pub packet_box: *const MpBox,
     pub tri_shading: *const MpTriShading,
     pub vertices: *const MpVertexShading,
+    pub materials: *const MpMaterial,
 }
 
 #[repr(C)]
@@ -171,6 +186,18 @@ pub struct MpHit {
     pub t: f32,
     pub u: f32,
     pub v: f32,
+}
+
+/// HitRecord (geometry/mod.rs:70-80); hit == 0 is Option::None.
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct MpHitRecord {
+    pub t: f32,
+    pub point: [f32; 3],
+    pub normal: [f32; 3],
+    pub material: u32,
+    pub texture_coords: [f32; 3],
+    pub hit: i32,
 }
 
 #[repr(C)]
@@ -254,6 +281,7 @@ extern "C" {
     pub fn mp_bvh_build_obj(path: *const c_char, quad_mode: c_int, out: *mut *mut MpFlatBvh) -> c_int;
     pub fn mp_bvh_build_mesh(positions: *const f32, normals: *const f32, n_vertices: u32, triangles: *const u32, n_triangles: u64, out: *mut *mut MpFlatBvh) -> c_int;
     pub fn mp_bvh_build_mesh_ex(positions: *const f32, normals: *const f32, n_vertices: u32, triangles: *const u32, n_triangles: u64, builder: c_int, out: *mut *mut MpFlatBvh) -> c_int;
+    pub fn mp_bvh_build_mesh_mat(positions: *const f32, normals: *const f32, texcoords: *const f32, n_vertices: u32, triangles: *const u32, tri_material: *const u32, n_triangles: u64, materials: *const MpMaterial, n_materials: u32, builder: c_int, out: *mut *mut MpFlatBvh) -> c_int;
     pub fn mp_bvh_free(bvh: *mut MpFlatBvh) -> c_int;
     pub fn mp_bvh_stats(bvh: *const MpFlatBvh, out: *mut MpBvhStats) -> c_int;
 
@@ -309,6 +337,7 @@ extern "C" {
     // Object::intersect on caller rays (scene/mod.rs:7-10) and CameraSampler::sample_ray dumps (camera.rs:176-191)
     pub fn mp_trace_rays(ctx: *mut MpCtx, host_rays: *const MpRay, n: u64, order: u32, host_out: *mut MpHit) -> c_int;
     pub fn mp_trace_rays_device(ctx: *mut MpCtx, dev_rays: *const MpRay, n: u64, order: u32, dev_out: *mut MpHit) -> c_int;
+    pub fn mp_intersect_rays(ctx: *mut MpCtx, host_rays: *const MpRay, n: u64, order: u32, host_out: *mut MpHitRecord) -> c_int;
     pub fn mp_generate_rays(ctx: *mut MpCtx, tiles: *const MpTile, n_tiles: u32, params: *const MpRenderParams, host_out: *mut MpRay, cap: u64, out_n: *mut u64) -> c_int;
 
     // raw memory helpers

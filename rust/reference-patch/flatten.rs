@@ -126,13 +126,14 @@ impl TriangleBvh {
             n_packets: packets.len() as u32,
             n_vertices: vertices.len() as u32,
             n_triangles,
-            _pad: 0,
+            n_materials: 0, // the reference writes material: 0 everywhere (building.rs:201): no table, constant grey
             inner: inner.as_ptr(),
             inner_box: inner_box.as_ptr(),
             packets: packets.as_ptr(),
             packet_box: packet_box.as_ptr(),
             tri_shading: shading.as_ptr(),
             vertices: vertices.as_ptr(),
+            materials: std::ptr::null(),
         };
         FlatBvh { raw, _inner: inner, _inner_box: inner_box, _packets: packets, _packet_box: packet_box, _shading: shading, _vertices: vertices }
     }

@@ -74,6 +74,8 @@ def load():
         "orc_resolve_rgba8": (None, [vp, u32, u32, u32, vp]),
         "orc_bvh_build_obj": (i, [C.c_char_p, i, P(P(_ffi.MpFlatBvh))]),
         "orc_bvh_build_mesh": (i, [vp, vp, u32, vp, u64, P(P(_ffi.MpFlatBvh))]),
+        "orc_bvh_build_mesh_mat": (i, [vp, vp, vp, u32, vp, vp, u64, vp, u32, P(P(_ffi.MpFlatBvh))]),
+        "orc_intersect_rays": (None, [P(_ffi.MpFlatBvh), vp, u64, u32, vp, i]),
         "orc_bvh_free": (None, [P(_ffi.MpFlatBvh)]),
         "orc_build_error": (C.c_char_p, []),
         "orc_brute_force": (None, [P(_ffi.MpFlatBvh), vp, u64, vp, i]),
@@ -84,6 +86,17 @@ def load():
         fn = getattr(o, name)
         fn.restype, fn.argtypes = res, args
     return o
+
+
+def materials_table(albedos, checker=None, checker_scale=None):
+    """MATERIAL_DTYPE rows for Oracle.build_mesh (the test side's own constructor of the table)."""
+    alb = np.asarray(albedos, np.float32).reshape(-1, 3)
+    m = np.zeros(len(alb), _ffi.MATERIAL_DTYPE)
+    m["albedo"] = alb
+    m["checker_scale"] = 4.0 if checker_scale is None else np.asarray(checker_scale, np.float32)
+    if checker is not None:
+        m["flags"] = np.asarray(checker, bool).astype(np.uint32)
+    return m
 
 
 class OracleBvh:
@@ -134,6 +147,13 @@ class OracleBvh:
     def vertices(self):
         return self._view("vertices", self.raw.n_vertices, np.float32, (8,))
 
+    def materials(self):
+        r = self.raw
+        if r.n_materials == 0:
+            return np.zeros(0, _ffi.MATERIAL_DTYPE)
+        buf = (C.c_char * (r.n_materials * _ffi.MATERIAL_DTYPE.itemsize)).from_address(C.cast(r.materials, C.c_void_p).value)
+        return np.frombuffer(buf, dtype=_ffi.MATERIAL_DTYPE)
+
     def stats(self):
         """Structural numbers of the tree, walked here in Python (the product's mp_bvh_stats is not used on this side)."""
         links, n_inner = self.inner_links(), self.raw.n_inner
@@ -165,14 +185,28 @@ class Oracle:
             raise RuntimeError("oracle builder: " + self.o.orc_build_error().decode())
         return OracleBvh(self.o, out)
 
-    def build_mesh(self, positions, triangles, normals=None):
+    def build_mesh(self, positions, triangles, normals=None, texcoords=None, tri_material=None, materials=None):
         pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
         tri = np.ascontiguousarray(triangles, np.uint32).reshape(-1, 3)
         nrm = None if normals is None else np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+        tex = None if texcoords is None else np.ascontiguousarray(texcoords, np.float32).reshape(-1, 2)
+        tm = None if tri_material is None else np.ascontiguousarray(tri_material, np.uint32).reshape(-1)
+        mats = None if materials is None else np.ascontiguousarray(materials, _ffi.MATERIAL_DTYPE).reshape(-1)
+        assert tex is None or len(tex) == len(pos)
+        assert tm is None or len(tm) == len(tri)
         out = C.POINTER(_ffi.MpFlatBvh)()
-        if self.o.orc_bvh_build_mesh(pos.ctypes.data, None if nrm is None else nrm.ctypes.data, len(pos), tri.ctypes.data, len(tri), C.byref(out)) != 0:
+        ptr = lambda a: None if a is None else a.ctypes.data  # noqa: E731
+        if self.o.orc_bvh_build_mesh_mat(pos.ctypes.data, ptr(nrm), ptr(tex), len(pos), tri.ctypes.data, ptr(tm), len(tri), ptr(mats),
+                                         0 if mats is None else len(mats), C.byref(out)) != 0:
             raise RuntimeError("oracle builder: " + self.o.orc_build_error().decode())
         return OracleBvh(self.o, out)
+
+    def intersect_rays(self, bvh, rays, order=0, threads=8):
+        """Object::intersect with finalisation for a batch: HIT_RECORD_DTYPE records."""
+        rays = np.ascontiguousarray(rays, RAY_DTYPE)
+        out = np.empty(len(rays), _ffi.HIT_RECORD_DTYPE)
+        self.o.orc_intersect_rays(bvh._ptr, rays.ctypes.data, len(rays), order, out.ctypes.data, threads)
+        return out
 
     def brute_force(self, bvh, rays, threads=8):
         rays = np.ascontiguousarray(rays, RAY_DTYPE)

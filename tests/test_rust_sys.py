@@ -58,7 +58,7 @@ def test_every_header_function_is_bound_with_the_same_arity():
 
 def test_constants_match_the_header():
     htext = _strip_c(open(HEADER).read())
-    hdr = {m.group(1): int(m.group(2).rstrip("u"), 0) for m in re.finditer(r"#define (MP_[A-Z0-9_]+) \(?(-?(?:0x[0-9A-Fa-f]+|\d+)u?)\)?", htext)}
+    hdr = {m.group(1): int(m.group(2).rstrip("u"), 0) for m in re.finditer(r"#define (MP_[A-Z0-9_]+) \(?(-?(?:0x[0-9A-Fa-f]+|\d+)u?)\)?(?![.\w])", htext)}
     rs = {m.group(1): int(m.group(2).replace("_", ""), 0) for m in re.finditer(r"pub const (MP_[A-Z0-9_]+): [a-z0-9_]+ = (-?(?:0x[0-9A-Fa-f_]+|\d+));", open(LIB_RS).read())}
     assert len(hdr) >= 30
     assert {k: (v, rs.get(k)) for k, v in hdr.items() if rs.get(k) != v} == {}
