@@ -160,7 +160,7 @@ def workload_config(name, args):
 
 def data_note(name):
     scene = WORKLOADS[name][0]
-    return "synthetic camera samples (counter-based RNG) on " + ("the reference's data/%s.obj" % scene if scene != "atrium" else
+    return "synthetic camera samples (counter-based RNG) on " + ("the reference's data/%s.obj" % scene if not scene.startswith("atrium") else
                                                                  "a procedural Sponza STAND-IN (sponza.obj is absent from the reference)")
 
 

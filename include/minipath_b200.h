@@ -138,6 +138,14 @@ int mp_bvh_build_mesh_ex(const float* positions, const float* normals, uint32_t 
 int mp_bvh_build_mesh_mat(const float* positions, const float* normals, const float* texcoords, uint32_t n_vertices,
                           const uint32_t* triangles, const uint32_t* tri_material, uint64_t n_triangles,
                           const MpMaterial* materials, uint32_t n_materials, int builder, MpFlatBvh** out);
+/* The same arguments, built ON THE GPU `device` (csrc/build_device.cu): Morton sort of the centroids, up to 8 children
+ * per node by radix splits, exact boxes bottom-up, then the reference's top-down round-out quantisation against the decompressed
+ * parent box (building.rs:134-155) and round-to-nearest leaf vertices (:183-195).  The node FORMAT and its quantisation rules are the
+ * reference's; the split is not (the reference's agglomerative SAH merge is sequential), so the tree differs from mp_bvh_build_*'s.
+ * out_device_ms (may be NULL): device time of the build, inputs resident, read-back excluded. */
+int mp_bvh_build_device(int device, const float* positions, const float* normals, const float* texcoords, uint32_t n_vertices,
+                        const uint32_t* triangles, const uint32_t* tri_material, uint64_t n_triangles,
+                        const MpMaterial* materials, uint32_t n_materials, MpFlatBvh** out, float* out_device_ms);
 int mp_bvh_free(MpFlatBvh* bvh);
 /* Structural statistics (node / packet counts, depth) — printing.rs:11-70 analogue, numbers only. */
 typedef struct MpBvhStats {

@@ -264,9 +264,12 @@ class TriangleBvh:
         check(lib.mp_bvh_build_obj(str(path).encode(), quad_mode, C.byref(out)))
         return cls(out)
 
+    BUILDER_REFERENCE, BUILDER_MEDIAN, BUILDER_DEVICE = 0, 1, 2
+
     @classmethod
-    def from_mesh(cls, positions, triangles, normals=None, builder=0, texcoords=None, tri_material=None, materials=None):
-        """Indexed mesh → BVH.  ``texcoords`` (n_vertices, 2), ``tri_material`` (n_triangles,) ids into ``materials``, a
+    def from_mesh(cls, positions, triangles, normals=None, builder=0, texcoords=None, tri_material=None, materials=None, device=0):
+        """Indexed mesh → BVH.  ``builder``: 0 the reference's split on the host, 1 median split on the host, 2 the device builder
+        (mp_bvh_build_device on GPU ``device``; ``last_build_ms`` then holds its device time).  ``texcoords`` (n_vertices, 2), ``tri_material`` (n_triangles,) ids into ``materials``, a
         MATERIAL_DTYPE array (see ``make_materials``); without ``materials`` the extension integrator shades a constant grey."""
         pos = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 3)
         tri = np.ascontiguousarray(triangles, dtype=np.uint32).reshape(-1, 3)
@@ -280,6 +283,15 @@ class TriangleBvh:
             raise ValueError("tri_material must have one id per triangle")
         out = C.POINTER(_ffi.MpFlatBvh)()
         fp, up = C.POINTER(C.c_float), C.POINTER(C.c_uint32)
+        if builder == cls.BUILDER_DEVICE:
+            ms = C.c_float()
+            check(lib.mp_bvh_build_device(device, pos.ctypes.data_as(fp), None if nrm is None else nrm.ctypes.data_as(fp),
+                                          None if tex is None else tex.ctypes.data_as(fp), len(pos), tri.ctypes.data_as(up),
+                                          None if tm is None else tm.ctypes.data_as(up), len(tri),
+                                          None if mats is None else mats.ctypes.data, 0 if mats is None else len(mats), C.byref(out), C.byref(ms)))
+            bvh = cls(out)
+            bvh.last_build_ms = ms.value
+            return bvh
         check(lib.mp_bvh_build_mesh_mat(pos.ctypes.data_as(fp), None if nrm is None else nrm.ctypes.data_as(fp),
                                         None if tex is None else tex.ctypes.data_as(fp), len(pos), tri.ctypes.data_as(up),
                                         None if tm is None else tm.ctypes.data_as(up), len(tri),

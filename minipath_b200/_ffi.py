@@ -37,6 +37,7 @@ PROTOTYPES = {
     "mp_bvh_build_mesh": (_i, [_P(C.c_float), _P(C.c_float), _u32, _P(_u32), _u64, _P(_P(MpFlatBvh))]),
     "mp_bvh_build_mesh_ex": (_i, [_P(C.c_float), _P(C.c_float), _u32, _P(_u32), _u64, _i, _P(_P(MpFlatBvh))]),
     "mp_bvh_build_mesh_mat": (_i, [_P(C.c_float), _P(C.c_float), _P(C.c_float), _u32, _P(_u32), _P(_u32), _u64, _vp, _u32, _i, _P(_P(MpFlatBvh))]),
+    "mp_bvh_build_device": (_i, [_i, _P(C.c_float), _P(C.c_float), _P(C.c_float), _u32, _P(_u32), _P(_u32), _u64, _vp, _u32, _P(_P(MpFlatBvh)), _P(C.c_float)]),
     "mp_bvh_free": (_i, [_P(MpFlatBvh)]),
     "mp_bvh_stats": (_i, [_P(MpFlatBvh), _P(MpBvhStats)]),
     "mp_camera_default": (_i, [_P(MpCamera)]),

@@ -33,19 +33,21 @@ fn main() {
             .arg("-o")
             .arg(out.join(format!("{name}.o"))));
     }
-    run(Command::new(&nvcc)
-        .args(["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",
-               "-prec-div=true", "-prec-sqrt=true", "-Xcompiler", "-fPIC,-ffp-contract=off", "-c"])
-        .arg(format!("-I{}", inc.display()))
-        .arg(cs.join("context.cu"))
-        .arg("-o")
-        .arg(out.join("context.o")));
+    for unit in ["context", "build_device"] {
+        run(Command::new(&nvcc)
+            .args(["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",
+                   "-prec-div=true", "-prec-sqrt=true", "-Xcompiler", "-fPIC,-ffp-contract=off", "-c"])
+            .arg(format!("-I{}", inc.display()))
+            .arg(cs.join(format!("{unit}.cu")))
+            .arg("-o")
+            .arg(out.join(format!("{unit}.o"))));
+    }
     let mut link = Command::new(&nvcc);
     link.args(["-shared", "-cudart", "static", "-o"]).arg(out.join("libminipath_b200.so"));
     for name in host {
         link.arg(out.join(format!("{name}.o")));
     }
-    link.arg(out.join("context.o")).args(["-lpthread", "-lrt", "-ldl"]);
+    link.arg(out.join("context.o")).arg(out.join("build_device.o")).args(["-lpthread", "-lrt", "-ldl"]);
     run(&mut link);
     println!("cargo:rustc-link-search=native={}", out.display());
     println!("cargo:rustc-link-lib=dylib=minipath_b200");

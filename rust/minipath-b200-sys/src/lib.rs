@@ -282,6 +282,7 @@ extern "C" {
     pub fn mp_bvh_build_mesh(positions: *const f32, normals: *const f32, n_vertices: u32, triangles: *const u32, n_triangles: u64, out: *mut *mut MpFlatBvh) -> c_int;
     pub fn mp_bvh_build_mesh_ex(positions: *const f32, normals: *const f32, n_vertices: u32, triangles: *const u32, n_triangles: u64, builder: c_int, out: *mut *mut MpFlatBvh) -> c_int;
     pub fn mp_bvh_build_mesh_mat(positions: *const f32, normals: *const f32, texcoords: *const f32, n_vertices: u32, triangles: *const u32, tri_material: *const u32, n_triangles: u64, materials: *const MpMaterial, n_materials: u32, builder: c_int, out: *mut *mut MpFlatBvh) -> c_int;
+    pub fn mp_bvh_build_device(device: c_int, positions: *const f32, normals: *const f32, texcoords: *const f32, n_vertices: u32, triangles: *const u32, tri_material: *const u32, n_triangles: u64, materials: *const MpMaterial, n_materials: u32, out: *mut *mut MpFlatBvh, out_device_ms: *mut f32) -> c_int;
     pub fn mp_bvh_free(bvh: *mut MpFlatBvh) -> c_int;
     pub fn mp_bvh_stats(bvh: *const MpFlatBvh, out: *mut MpBvhStats) -> c_int;
 

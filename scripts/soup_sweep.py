@@ -4,8 +4,9 @@
 Mrays/s, visits per ray, algorithmic bytes per ray and the fraction of the L2 / HBM roofs.
 
     python scripts/soup_sweep.py --sizes 1e6,1e7 --rays 4194304
-The BVH comes from the median-split builder (builder=1; the reference split is O(G^3) per node and not usable at this size);
-it emits the reference node format, so the traversal kernels and their parity tests are the same.
+--builders picks who makes the tree: `device` (mp_bvh_build_device, csrc/build_device.cu), `median` (host median split, builder=1) or
+`reference` (the reference's agglomerative split on all host threads, builder=0; minutes above 1e6 triangles).  All three emit the
+reference node format, so the traversal kernels and their parity tests are the same; the line names the builder.
 """
 import argparse
 import json
@@ -24,6 +25,8 @@ def main():
     ap.add_argument("--sizes", default="1e6,1e7")
     ap.add_argument("--rays", type=int, default=1 << 22)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--builders", default="device,median")
+    ap.add_argument("--kernels", default="thread-decoded,thread-quantised,pool-quantised,pool-decoded")
     args = ap.parse_args()
     import torch
 
@@ -41,11 +44,16 @@ def main():
     ctx.set_stream(stream.cuda_stream)
     l2 = ctx.probe_l2_gbs(32 << 20)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    for size in [int(float(x)) for x in args.sizes.split(",")]:
-        t0 = time.time()
+    builder_ids = {"reference": 0, "median": 1, "device": 2}
+    builder_names = {"reference": "reference split on the host (builder=0)", "median": "median split on the host (builder=1)", "device": "device builder (mp_bvh_build_device)"}
+    kernels = {"thread-decoded": ("thread", mp.TRACE_THREAD, mp.LAYOUT_DECODED), "thread-quantised": ("thread", mp.TRACE_THREAD, mp.LAYOUT_QUANTISED),
+               "pool-quantised": ("pool", mp.TRACE_POOL, mp.LAYOUT_QUANTISED), "pool-decoded": ("pool", mp.TRACE_POOL, mp.LAYOUT_DECODED)}
+    for size, bname in [(int(float(x)), b) for x in args.sizes.split(",") for b in args.builders.split(",")]:
         pos, tri = scenes.soup_mesh(size)
-        bvh = mp.TriangleBvh.from_mesh(pos, tri, builder=1)
+        t0 = time.time()
+        bvh = mp.TriangleBvh.from_mesh(pos, tri, builder=builder_ids[bname])
         build_s = time.time() - t0
+        build_device_ms = getattr(bvh, "last_build_ms", None)
         st = bvh.stats()
         bmin, bmax = bvh.get_bounding_box()
         o, d = scenes.incoherent_rays(bmin, bmax, args.rays)
@@ -55,8 +63,7 @@ def main():
         rays = torch.from_numpy(np.concatenate([o, d, inv], 1).astype(np.float32)).cuda()
         hits = torch.empty((args.rays, 4), dtype=torch.int32, device="cuda")
         scene_mb = (st["n_inner"] * 160 + st["n_packets"] * 192) / 1e6
-        for vname, variant, layout in (("thread", mp.TRACE_THREAD, mp.LAYOUT_DECODED), ("thread", mp.TRACE_THREAD, mp.LAYOUT_QUANTISED),
-                                       ("pool", mp.TRACE_POOL, mp.LAYOUT_QUANTISED), ("pool", mp.TRACE_POOL, mp.LAYOUT_DECODED)):
+        for vname, variant, layout in [kernels[k] for k in args.kernels.split(",")]:
             ctx.set_trace_variant(variant)
             ctx.set_node_layout(layout)
             ctx.upload_scene(bvh)
@@ -85,7 +92,8 @@ def main():
                     "mrays_s": n / t / 1e6, "ms": t * 1e3, "inner_per_ray": cnt["inner_visits"] / n, "packets_per_ray": cnt["packet_visits"] / n,
                     "bytes_per_ray": bytes_ray, "hit_fraction": hit_frac, "scene_mb": scene_mb, "bvh": {k: st[k] for k in ("n_inner", "n_leaves", "n_packets", "max_depth")},
                     "algorithmic_gbs": bytes_ray * n / t / 1e9, "frac_of_l2": bytes_ray * n / t / 1e9 / l2, "frac_of_hbm": bytes_ray * n / t / 1e9 / hbm,
-                    "l2_probe_gbs": l2, "hbm_gbs": hbm, "builder": "median-split (builder=1)", "build_s": build_s, "l2": "flushed between reps"}
+                    "l2_probe_gbs": l2, "hbm_gbs": hbm, "builder": builder_names[bname], "build_s": build_s, "build_device_ms": build_device_ms,
+                    "leaves_per_ray": cnt["leaf_visits"] / n, "leaf_fill": st["mean_leaf_fill"], "l2": "flushed between reps"}
             print(json.dumps(line), flush=True)
         del rays, hits
     ctx.close()
