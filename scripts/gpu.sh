@@ -16,7 +16,9 @@ mkdir -p gpurun_out
 task=$1; shift
 case $task in
   tests)
-    timeout 1500 python -m pytest tests -m gpu -x -q "$@" 2>&1 | tail -15 | tee gpurun_out/tests.txt ;;
+    # paths / options given: only those (e.g. tests/test_gpu_builder.py -s); none: the whole GPU suite
+    if [ $# -gt 0 ]; then timeout 1500 python -m pytest -m gpu -x -q "$@" 2>&1 | tail -40 | tee gpurun_out/tests.txt
+    else timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 | tee gpurun_out/tests.txt; fi ;;
   bench)
     tag=$1; shift
     timeout 900 python bench.py "$@" > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err || tail -5 gpurun_out/${tag}_bench.err
