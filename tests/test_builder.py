@@ -56,3 +56,44 @@ def test_links_are_in_range_and_cover_every_triangle():
     sh = np.asarray(bvh.tri_shading()).view(np.uint32).reshape(-1, 4)  # v0, v1, v2, flags|material; padding lanes are all zero
     real = sh[sh[:, 1] != 0]                                           # soup_mesh: triangle i owns vertices 3i..3i+2
     assert len(real) == 200_000 and len(np.unique(real[:, 0] // 3)) == 200_000
+
+
+def test_stats_rejects_malformed_trees():
+    """mp_bvh_stats is what mp_scene_upload / mp_render validate a caller-made MpFlatBvh with: links out of range, a node with two
+    parents (a cycle), leaves that overlap and vertex ids out of range are MP_EINVAL, not a host crash."""
+    import ctypes as C
+    import os
+
+    import minipath_b200 as mp
+    from minipath_b200 import _ffi
+
+    bvh = mp.TriangleBvh.with_obj(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "data", "teapot.obj"))
+    good = bvh.stats()
+    assert good["n_inner"] == bvh.raw.n_inner and good["n_packets"] == bvh.raw.n_packets
+    links = bvh.inner_links()  # writable view of the library-owned array
+    sh = bvh.tri_shading()
+
+    def bad():
+        s = _ffi.MpBvhStats()
+        rc = _ffi.lib.mp_bvh_stats(bvh._ptr, C.byref(s))
+        return rc
+
+    lane = int(np.nonzero(links[0] != _ffi.LINK_NULL)[0][0])
+    keep = int(links[0, lane])
+    for wrong in ((bvh.raw.n_inner + 5) << 3, 0 << 3, ((bvh.raw.n_packets - 1) << 3) | 3):  # out of range, back to the root (cycle), leaf past the end
+        links.flags.writeable = True
+        links[0, lane] = wrong
+        assert bad() == _ffi.MP_EINVAL, hex(wrong)
+        links[0, lane] = keep
+    assert bad() == _ffi.MP_OK
+    other = [int(k) for k in links[0] if int(k) != _ffi.LINK_NULL and int(k) != keep]
+    if other:
+        links[0, lane] = other[0]  # two parents for one subtree
+        assert bad() == _ffi.MP_EINVAL
+        links[0, lane] = keep
+    sh.flags.writeable = True
+    v = int(sh[0, 0])
+    sh[0, 0] = bvh.raw.n_vertices
+    assert bad() == _ffi.MP_EINVAL
+    sh[0, 0] = v
+    assert bad() == _ffi.MP_OK
