@@ -73,24 +73,32 @@ __device__ __forceinline__ Ray ray_new(F3 origin, F3 direction) {
 }
 
 // Counter-based RNG shared with the CPU oracle (the reference's SmallRng is OS-seeded, worker.rs:25, so only the
-// distributions of camera.rs:178-184 are reproduced): PCG-RXS-M-XS 32.
+// distributions of camera.rs:178-184 are reproduced): PCG-RXS-M-XS 32 with 64 bits per path — the 32-bit LCG state AND its own
+// odd increment (the PCG "stream"), two independent hashes of (pixel, sample, seed).  One shared increment would make all paths
+// windows of ONE 2^32-long sequence: a 4K x 1024 spp frame has 8.5e9 paths, more than that sequence has starting points.
 __device__ __forceinline__ uint32_t pcg_hash(uint32_t v) {
     uint32_t s = v * 747796405u + 2891336453u;
     uint32_t w = ((s >> ((s >> 28) + 4u)) ^ s) * 277803737u;
     return (w >> 22) ^ w;
 }
-__device__ __forceinline__ uint32_t rng_init(uint32_t pixel_index, uint32_t sample_index, uint32_t seed_hash) {
-    return pcg_hash(pixel_index ^ pcg_hash(sample_index ^ seed_hash));
+struct Rng {
+    uint32_t state, inc;
+};
+__device__ __forceinline__ Rng rng_init(uint32_t pixel_index, uint32_t sample_index, uint32_t seed_hash) {
+    Rng r;
+    r.state = pcg_hash(pixel_index ^ pcg_hash(sample_index ^ seed_hash));
+    r.inc = pcg_hash(sample_index ^ pcg_hash(pixel_index ^ ~seed_hash)) | 1u;
+    return r;
 }
-__device__ __forceinline__ uint32_t rng_next(uint32_t& state) {
-    uint32_t s = state * 747796405u + 2891336453u;
-    state = s;
+__device__ __forceinline__ uint32_t rng_next(Rng& r) {
+    uint32_t s = r.state * 747796405u + r.inc;
+    r.state = s;
     uint32_t w = ((s >> ((s >> 28) + 4u)) ^ s) * 277803737u;
     return (w >> 22) ^ w;
 }
-__device__ __forceinline__ float u01(uint32_t& s) { return __fmul_rn((float)(rng_next(s) >> 8), 1.0f / 16777216.0f); }
+__device__ __forceinline__ float u01(Rng& s) { return __fmul_rn((float)(rng_next(s) >> 8), 1.0f / 16777216.0f); }
 // rand_distr::UnitDisc: rejection sampling
-__device__ __forceinline__ void unit_disc(uint32_t& s, float& x, float& y) {
+__device__ __forceinline__ void unit_disc(Rng& s, float& x, float& y) {
     for (;;) {
         float a = __fsub_rn(__fmul_rn(2.0f, u01(s)), 1.0f);
         float b = __fsub_rn(__fmul_rn(2.0f, u01(s)), 1.0f);
@@ -107,7 +115,7 @@ struct Camera {  // CameraSampler (camera.rs:26-39)
 };
 
 // CameraSampler::sample_ray (camera.rs:176-191)
-__device__ __forceinline__ Ray sample_ray(const Camera& c, uint32_t px, uint32_t py, uint32_t& rng) {
+__device__ __forceinline__ Ray sample_ray(const Camera& c, uint32_t px, uint32_t py, Rng& rng) {
     float film_u = __fadd_rn((float)px, __fsub_rn(u01(rng), 0.5f));
     float film_v = __fadd_rn((float)py, __fsub_rn(u01(rng), 0.5f));
     F3 fp = (c.film_origin_offset + c.up * __fmul_rn(film_v, c.pixel_scale)) - c.right * __fmul_rn(film_u, c.pixel_scale);

@@ -105,7 +105,7 @@ __device__ __forceinline__ bool map_pixel32(const TileMap& tm, uint32_t gid, uin
 }
 
 // Cosine-weighted direction around n: Malley's method on rand_distr's unit disc, frame after Duff et al. 2017 (oracle: render_sample).
-__device__ __forceinline__ F3 bounce_direction(const F3& n, uint32_t& rng) {
+__device__ __forceinline__ F3 bounce_direction(const F3& n, Rng& rng) {
     float x, y;
     unit_disc(rng, x, y);
     const float z = __fsqrt_rn(fmaxf(0.0f, __fsub_rn(1.0f, __fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)))));
@@ -119,7 +119,7 @@ __device__ __forceinline__ F3 bounce_direction(const F3& n, uint32_t& rng) {
 
 // The bounce loop of render_sample with a material table (oracle/oracle_render.inc: render_sample).
 template <int LAYOUT, int ORDER, bool COUNT>
-__device__ __noinline__ float4 render_sample_rgb(const Scene& sc, Ray ray, uint32_t rng, uint32_t max_bounces, ThreadCounts& tc) {
+__device__ __noinline__ float4 render_sample_rgb(const Scene& sc, Ray ray, Rng rng, uint32_t max_bounces, ThreadCounts& tc) {
     F3 T = f3(1.0f, 1.0f, 1.0f), L = f3(0.0f, 0.0f, 0.0f);
     float alpha = 0.0f;
     for (uint32_t depth = 0;; ++depth) {
@@ -161,7 +161,7 @@ __device__ __noinline__ float4 render_sample_rgb(const Scene& sc, Ray ray, uint3
 template <int LAYOUT, int ORDER, bool COUNT, bool RGB>
 __device__ __forceinline__ float4 render_sample(const Scene& sc, const Camera& cam, uint32_t px, uint32_t py, uint32_t pixel_index,
                                                 uint32_t sample, uint32_t seed_hash, uint32_t max_bounces, ThreadCounts& tc) {
-    uint32_t rng = rng_init(pixel_index, sample, seed_hash);
+    Rng rng = rng_init(pixel_index, sample, seed_hash);
     Ray ray = sample_ray(cam, px, py, rng);
     tc.camera_rays++;
     if (max_bounces == 0) {
@@ -297,7 +297,7 @@ __global__ void __launch_bounds__(128) generate_rays_kernel(Camera cam, TileMap 
     const MpTile t = tm.tiles[ti];
     const unsigned long long local = (unsigned long long)(y - t.min_y) * (t.max_x - t.min_x) + (x - t.min_x);
     for (uint32_t s = 0; s < sample_count; ++s) {
-        uint32_t rng = rng_init(y * width + x, sample_base + s, seed_hash);
+        Rng rng = rng_init(y * width + x, sample_base + s, seed_hash);
         const Ray r = sample_ray(cam, x, y, rng);
         float* p = out + 9 * ((tile_offsets[ti] + local) * sample_count + s);
         p[0] = r.o.x, p[1] = r.o.y, p[2] = r.o.z, p[3] = r.d.x, p[4] = r.d.y, p[5] = r.d.z, p[6] = r.inv.x, p[7] = r.inv.y, p[8] = r.inv.z;

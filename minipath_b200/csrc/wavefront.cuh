@@ -16,7 +16,7 @@ struct WavefrontBuffers {
     float4* ray_o = nullptr;      // origin.xyz, throughput T
     float4* ray_d = nullptr;      // unit direction.xyz, radiance L
     uint4* hit = nullptr;         // tri, t, u, v
-    uint4* meta = nullptr;        // pixel_index, rng state, depth | alpha << 31, unused
+    uint4* meta = nullptr;        // pixel_index, rng state, depth | alpha << 31, rng increment
     uint32_t* queue[2] = {nullptr, nullptr};
     float4* sh_o = nullptr;       // shadow ray origin.xyz, contribution
     uint32_t* sh_path = nullptr;
@@ -121,11 +121,11 @@ __global__ void __launch_bounds__(WF_STAGE_THREADS) wf_raygen_kernel(Camera cam,
     ThreadCounts tc{};
     if (active) {
         const uint32_t pixel_index = y * width + x;
-        uint32_t rng = rng_init(pixel_index, sample_first + s, seed_hash);
+        Rng rng = rng_init(pixel_index, sample_first + s, seed_hash);
         const Ray r = sample_ray(cam, x, y, rng);
         ray_o[gid] = make_float4(r.o.x, r.o.y, r.o.z, 1.0f);
         ray_d[gid] = make_float4(r.d.x, r.d.y, r.d.z, 0.0f);
-        meta[gid] = make_uint4(pixel_index, rng, 0u, 0u);
+        meta[gid] = make_uint4(pixel_index, rng.state, 0u, rng.inc);
         if (rgb) rgb[gid] = make_float4(1.0f, 1.0f, 0.0f, 0.0f);
         tc.camera_rays = 1;
     }
@@ -233,8 +233,9 @@ __global__ void __launch_bounds__(WF_STAGE_THREADS) wf_shade_kernel(Scene sc, co
                     if (RGB) sc2 = make_float2(__fmul_rn(__fmul_rn(e.x, EXT_SUN_E), c), __fmul_rn(__fmul_rn(e.y, EXT_SUN_E), c));
                 }
                 survive = true;
+                Rng rng{m.y, m.w};
                 if (depth >= EXT_RR_START) {
-                    const float q = u01(m.y);
+                    const float q = u01(rng);
                     const float ps = RGB ? fmaxf(fmaxf(T, e.x), e.y) : T;
                     if (q >= ps) {
                         survive = false;
@@ -244,7 +245,8 @@ __global__ void __launch_bounds__(WF_STAGE_THREADS) wf_shade_kernel(Scene sc, co
                     }
                 }
                 if (survive) {
-                    const Ray nr = ray_new(origin, bounce_direction(nrm, m.y));
+                    const Ray nr = ray_new(origin, bounce_direction(nrm, rng));
+                    m.y = rng.state;
                     ray_o[path] = make_float4(nr.o.x, nr.o.y, nr.o.z, T);
                     ray_d[path] = make_float4(nr.d.x, nr.d.y, nr.d.z, L);
                     if (RGB) rgb[path] = e;
@@ -313,13 +315,13 @@ __global__ void __launch_bounds__(128, WF_PRIMARY_MIN_BLOCKS) wf_primary_kernel(
     float4 e = make_float4(1.0f, 1.0f, 0.0f, 0.0f);  // T.g, T.b, L.g, L.b
     if (active) {
         const uint32_t pixel_index = y * width + x;
-        uint32_t rng = rng_init(pixel_index, sample_first + s, seed_hash);
+        Rng rng = rng_init(pixel_index, sample_first + s, seed_hash);
         const Ray r = sample_ray(cam, x, y, rng);
         tc.camera_rays = 1, tc.rays = 1;
         const Hit h = trace<LAYOUT, ORDER, COUNT>(sc, r, false, tc.vis);
         // ---- wf_shade_kernel at depth 0 (T = 1, L = 0) ----
         float T = 1.0f, L = 0.0f;
-        m = make_uint4(pixel_index, rng, 0u, 0u);
+        m = make_uint4(pixel_index, rng.state, 0u, rng.inc);
         out_d = make_float4(r.d.x, r.d.y, r.d.z, 0.0f);
         if (max_bounces == 0) {  // the reference shader (worker.rs:57-64)
             if (h.tri != MP_NO_HIT) {
@@ -352,7 +354,8 @@ __global__ void __launch_bounds__(128, WF_PRIMARY_MIN_BLOCKS) wf_primary_kernel(
                 survive = true;  // Russian roulette starts at depth EXT_RR_START >= 1
                 static_assert(EXT_RR_START >= 1u, "depth 0 never plays Russian roulette");
                 {
-                    const Ray nr = ray_new(origin, bounce_direction(nrm, m.y));
+                    const Ray nr = ray_new(origin, bounce_direction(nrm, rng));
+                    m.y = rng.state;
                     ray_o[gid] = make_float4(nr.o.x, nr.o.y, nr.o.z, T);
                     out_d = make_float4(nr.d.x, nr.d.y, nr.d.z, L);
                     m.z = (m.z & 0x80000000u) | 1u;

@@ -153,15 +153,16 @@ uint32_t orc_pcg_hash(uint32_t v) {
     uint32_t w = ((s >> ((s >> 28) + 4u)) ^ s) * 277803737u;
     return (w >> 22) ^ w;
 }
-uint32_t orc_rng_init(uint32_t pixel_index, uint32_t sample_index, uint64_t seed) {
+// 64 bits per path: rng[0] = the LCG state, rng[1] = its odd increment (the PCG stream) — two hashes of (pixel, sample, seed)
+void orc_rng_init(uint32_t pixel_index, uint32_t sample_index, uint64_t seed, uint32_t rng[2]) {
     uint32_t h = orc_pcg_hash((uint32_t)(seed >> 32));
-    h = orc_pcg_hash((uint32_t)seed ^ h);
-    h = orc_pcg_hash(sample_index ^ h);
-    return orc_pcg_hash(pixel_index ^ h);
+    h = orc_pcg_hash((uint32_t)seed ^ h);  // the 32-bit seed hash both sides start from
+    rng[0] = orc_pcg_hash(pixel_index ^ orc_pcg_hash(sample_index ^ h));
+    rng[1] = orc_pcg_hash(sample_index ^ orc_pcg_hash(pixel_index ^ ~h)) | 1u;
 }
-uint32_t orc_rng_next(uint32_t* state) {
-    uint32_t s = *state * 747796405u + 2891336453u;
-    *state = s;
+uint32_t orc_rng_next(uint32_t rng[2]) {
+    uint32_t s = rng[0] * 747796405u + rng[1];
+    rng[0] = s;
     uint32_t w = ((s >> ((s >> 28) + 4u)) ^ s) * 277803737u;
     return (w >> 22) ^ w;
 }

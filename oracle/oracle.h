@@ -57,8 +57,8 @@ uint8_t orc_color_channel_to_u8(float c);
 
 /* ---- counter-based RNG shared with the CUDA path (the reference's SmallRng is OS-seeded) ---- */
 uint32_t orc_pcg_hash(uint32_t v);
-uint32_t orc_rng_init(uint32_t pixel_index, uint32_t sample_index, uint64_t seed);
-uint32_t orc_rng_next(uint32_t* state);
+void orc_rng_init(uint32_t pixel_index, uint32_t sample_index, uint64_t seed, uint32_t rng[2]);
+uint32_t orc_rng_next(uint32_t rng[2]);
 
 /* ---- the path ---- */
 /* 0 = scalar lane loops, 1 = AVX2+FMA intrinsics (bit-identical; the CPU baseline uses 1) */

@@ -61,7 +61,7 @@ def load():
         "orc_link_decode": (i, [u32, P(i), P(u32), P(u32)]),
         "orc_color_channel_to_u8": (C.c_uint8, [f]),
         "orc_pcg_hash": (u32, [u32]),
-        "orc_rng_init": (u32, [u32, u32, u64]),
+        "orc_rng_init": (None, [u32, u32, u64, P(u32)]),
         "orc_rng_next": (u32, [P(u32)]),
         "orc_set_simd": (None, [i]),
         "orc_get_simd": (i, []),

@@ -203,9 +203,10 @@ def test_camera_left_right_up_down(oracle):
     s = cam.build_sampler((800, 600))
 
     def ray(px, py, k):
-        state = C.c_uint32(oracle.o.orc_rng_init(py * 800 + px, k, 123))
+        state = (C.c_uint32 * 2)()
+        oracle.o.orc_rng_init(py * 800 + px, k, 123, state)
         r = mp._ffi.MpRay()
-        oracle.o.orc_sample_ray(C.byref(s), px, py, C.byref(state), C.byref(r))
+        oracle.o.orc_sample_ray(C.byref(s), px, py, state, C.byref(r))
         return np.array(list(r.direction), F)
 
     for k in range(20):
