@@ -78,7 +78,7 @@ def parse_args():
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel")
     ap.add_argument("--bounces", type=int, default=-1, help="override the workload's max_bounces")
     ap.add_argument("--shard", default="tiles", choices=["tiles", "spp"], help="N>1: dynamic tile queue (strong scaling) or sample split (weak)")
-    ap.add_argument("--min-batch", type=int, default=4, help="N>1 tile sharding: smallest batch of tiles a GPU claims")
+    ap.add_argument("--min-batch", type=int, default=0, help="N>1 tile sharding: smallest batch of tiles a GPU claims (0 = the library's choice: about 2^20 paths)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the teapot-1080p (configs[1]) rider")

@@ -10,7 +10,8 @@
 // What is different: the SPLIT.  The reference runs a binned agglomerative SAH merge per node (building.rs:238-345), a sequential
 // O(bins^3) loop; here the triangles are sorted once along a 63-bit Morton curve of their centroids and every node cuts its range of
 // that order into up to 8 children: three rounds of radix splits (the highest differing Morton bit, Karras 2012) while a node holds
-// more than 8 full leaves, equal runs of whole packets when it can be covered by at most 8 leaves.  The tree is therefore NOT the
+// more than 8 leaves' worth of triangles, equal runs of whole packets when it can be covered by at most 8 leaves (a leaf holds up to
+// DEVICE_LEAF_DEFAULT triangles, not the format's 56: a visited leaf tests all its packets).  The tree is therefore NOT the
 // reference's tree — its quality is measured against it (visits per ray, tests/test_gpu_builder.py, profiles/) — but any traversal
 // of it follows the same rules and gives the same bits on CPU and GPU.
 //
@@ -143,11 +144,14 @@ __device__ __forceinline__ uint32_t radix_split(const unsigned long long* __rest
     return hi;
 }
 
-#define LEAF_MAX MP_LEAF_MAX_TRIANGLES
+// Triangles a leaf may hold.  The format allows 56 (7 packets, mod.rs:16-17), but a visited leaf tests ALL its packets: the reference's
+// cost model (0.75 per packet against 1 per inner node, building.rs:358-383) ends up near 2 packets per leaf on real scenes, and so does
+// this default (measured in profiles/r2g_device_builder_leaf_size.txt).  MINIPATH_B200_DEVICE_LEAF overrides it (8..56, a multiple of 8).
+#define DEVICE_LEAF_DEFAULT 16u
 
 // Children of every node of one level.  node_range[first + k] is the Morton range of the level's k-th node.
 __global__ void __launch_bounds__(128) split_kernel(const unsigned long long* __restrict__ keys, const Range* __restrict__ node_range, uint32_t first,
-                                                    uint32_t count, NodeTopo* __restrict__ topo, uint32_t* __restrict__ n_inner, uint32_t* __restrict__ n_packets) {
+                                                    uint32_t count, uint32_t LEAF_MAX, NodeTopo* __restrict__ topo, uint32_t* __restrict__ n_inner, uint32_t* __restrict__ n_packets) {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= count) return;
     const Range r = node_range[first + k];
@@ -197,7 +201,7 @@ __global__ void __launch_bounds__(128) split_kernel(const unsigned long long* __
 
 // Child indices from the scanned counts: inner children become the nodes next_first + inner_off[k] .., leaves take packets from
 // packet_first + packet_off[k] on and a slot of `leaves` from leaf_first + leaf_off.. (leaf_off is scanned separately).
-__global__ void __launch_bounds__(128) assign_kernel(NodeTopo* __restrict__ topo, Range* __restrict__ node_range, uint32_t first, uint32_t count,
+__global__ void __launch_bounds__(128) assign_kernel(NodeTopo* __restrict__ topo, Range* __restrict__ node_range, uint32_t first, uint32_t count, uint32_t LEAF_MAX,
                                                      const uint32_t* __restrict__ inner_off, const uint32_t* __restrict__ packet_off, uint32_t next_first,
                                                      uint32_t packet_first, Leaf* __restrict__ leaves, uint32_t* __restrict__ leaf_count,
                                                      uint32_t* __restrict__ parent_slot) {
@@ -379,6 +383,12 @@ extern "C" int mp_bvh_build_device(int device, const float* positions, const flo
     if (n_triangles == 0) return mp::fail(MP_EINVAL, "scene has no triangles (reference asserts in build_leaf, building.rs:178)");
     if (n_triangles > 0x7fffffffull / 8) return mp::fail(MP_EINVAL, "too many triangles for the 29-bit link index range (mod.rs:71)");
     const uint32_t nt = (uint32_t)n_triangles;
+    uint32_t LEAF_MAX = DEVICE_LEAF_DEFAULT;
+    if (const char* e = getenv("MINIPATH_B200_DEVICE_LEAF")) {
+        const long v = atol(e);
+        if (v < 8 || v > MP_LEAF_MAX_TRIANGLES || v % 8) return mp::fail(MP_EINVAL, "MINIPATH_B200_DEVICE_LEAF must be a multiple of 8 in 8..56");
+        LEAF_MAX = (uint32_t)v;
+    }
     for (uint64_t i = 0; i < 3 * n_triangles; ++i)
         if (triangles[i] >= n_vertices) return mp::fail(MP_EINVAL, "triangle %llu references vertex %u >= %u", (unsigned long long)(i / 3), triangles[i], n_vertices);
     if (tri_material)
@@ -494,7 +504,7 @@ extern "C" int mp_bvh_build_device(int device, const float* positions, const flo
         while (count > 0) {
             levels.emplace_back(first, count);
             const unsigned blocks = (count + 127) / 128;
-            split_kernel<<<blocks, 128, 0, st>>>(d_keys_sorted, d_node_range, first, count, d_topo, d_cnt_inner, d_cnt_packets);
+            split_kernel<<<blocks, 128, 0, st>>>(d_keys_sorted, d_node_range, first, count, LEAF_MAX, d_topo, d_cnt_inner, d_cnt_packets);
             // one extra element so that the last entry of the exclusive scan is the level's total
             CKB(cudaMemsetAsync(d_cnt_inner + count, 0, sizeof(uint32_t), st));
             CKB(cudaMemsetAsync(d_cnt_packets + count, 0, sizeof(uint32_t), st));
@@ -505,7 +515,7 @@ extern "C" int mp_bvh_build_device(int device, const float* positions, const flo
             CKB(cudaMemcpyAsync(&totals[1], d_off_packets + count, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
             CKB(cudaStreamSynchronize(st));
             if ((size_t)n_inner + totals[0] > node_cap) return mp::fail(MP_EINVAL, "device builder: node capacity exceeded");
-            assign_kernel<<<blocks, 128, 0, st>>>(d_topo, d_node_range, first, count, d_off_inner, d_off_packets, n_inner, n_packets, d_leaves, d_leaf_count,
+            assign_kernel<<<blocks, 128, 0, st>>>(d_topo, d_node_range, first, count, LEAF_MAX, d_off_inner, d_off_packets, n_inner, n_packets, d_leaves, d_leaf_count,
                                                   d_parent_slot);
             first = n_inner, count = totals[0];
             n_inner += totals[0], n_packets += totals[1];

@@ -340,7 +340,10 @@ int mp_group_render(MpGroup* g, const MpTile* tiles, uint32_t n_tiles, const MpR
     if (shard > MP_SHARD_SPP) return fail(MP_EINVAL, "bad sharding scheme %u", shard);
     if (!g->width) return fail(MP_ESTATE, "no film (mp_group_film_create)");
     if (n_tiles == 0) return fail(MP_EINVAL, "empty tile list");
-    if (min_batch == 0) min_batch = 4;
+    if (min_batch == 0) {  // auto: the smallest batch still carries about a million paths (a 64x64 tile at 256 spp is one)
+        const uint64_t per_tile = (uint64_t)std::max(1u, params->tile_size) * std::max(1u, params->tile_size) * std::max(1u, params->sample_count);
+        min_batch = (uint32_t)std::max<uint64_t>(1, (((uint64_t)1 << 20) + per_tile - 1) / per_tile);
+    }
     if (shard == MP_SHARD_TILES) {
         if (g->queue) {  // every rank has left the previous render's claim loop before rank 0 rewinds the counter
             if (int rc = mp_tileq_barrier(g->queue, (uint32_t)g->world, 120000)) return rc;

@@ -287,7 +287,8 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
     {
         const size_t paths_per_tile = (size_t)settings->tile_size * settings->tile_size * settings->sample_count;
         const size_t pass_tiles = ((size_t)1 << 25) / std::max<size_t>(1, paths_per_tile);
-        p->min_batch = devs.size() == 1 ? std::max<size_t>(4, pass_tiles) : 4;
+        // several devices: the tail batches shrink to about a million paths each, so that the devices finish together
+        p->min_batch = devs.size() == 1 ? std::max<size_t>(4, pass_tiles) : std::max<size_t>(1, (((size_t)1 << 20) + paths_per_tile - 1) / std::max<size_t>(1, paths_per_tile));
         p->batch = settings->tiles_per_batch;
     }
     p->started = started, p->finished = finished, p->user = user;

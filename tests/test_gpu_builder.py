@@ -153,26 +153,36 @@ def test_bad_input_is_rejected():
 QUALITY_FACTOR = 2.0  # sectors gathered per ray on the device-built tree, at most this multiple of the host reference-split tree's
 
 
+def _visits(ctx, bvh, rays):
+    ctx.upload_scene(bvh)
+    ctx.enable_counters(True)
+    ctx.reset_counters()
+    hits = ctx.trace_rays(rays)
+    c = ctx.counters()
+    ctx.enable_counters(False)
+    st = bvh.stats()
+    return {"inner": round(c["inner_visits"] / len(rays), 2), "packets": round(c["packet_visits"] / len(rays), 2), "hits": int((hits["tri"] != mp.NO_HIT).sum()),
+            "sectors": round((5 * c["inner_visits"] + 6 * c["packet_visits"]) / len(rays), 2), "n_inner": st["n_inner"], "n_leaves": st["n_leaves"],
+            "n_packets": st["n_packets"], "leaf_fill": round(st["mean_leaf_fill"], 3)}
+
+
 @pytest.mark.parametrize("name", ["teapot", "atrium"])
-def test_quality_next_to_the_reference_split(oracle, name):
+def test_quality_next_to_the_reference_split(oracle, name, monkeypatch):
     """Visits per ray (camera + incoherent rays) on the device-built tree and on the host reference-split tree, as L1 sectors
-    (5 per node record, 6 per packet record: SURVEY §8(d))."""
+    (5 per node record, 6 per packet record: SURVEY §8(d)); the leaf-size knob of the device builder is swept beside the default."""
     pos, tri, nrm, dev = _built(name)
     host = mp.TriangleBvh.from_mesh(pos, tri, normals=nrm, builder=0)
     rays = _rays(oracle, dev, 256 * 256, 60000, seed=23)
     ctx = mp.Context(0)
     ctx.set_trace_variant(mp.TRACE_POOL)
-    out = {}
-    for label, bvh in (("device", dev), ("host", host)):
-        ctx.upload_scene(bvh)
-        ctx.enable_counters(True)
-        ctx.reset_counters()
-        hits = ctx.trace_rays(rays)
-        c = ctx.counters()
-        ctx.enable_counters(False)
-        out[label] = {"inner": c["inner_visits"] / len(rays), "packets": c["packet_visits"] / len(rays), "hits": int((hits["tri"] != mp.NO_HIT).sum()),
-                      "sectors": (5 * c["inner_visits"] + 6 * c["packet_visits"]) / len(rays), "stats": bvh.stats()}
+    out = {"host reference split": _visits(ctx, host, rays), "device (default leaf size)": _visits(ctx, dev, rays)}
+    for leaf in (8, 16, 24, 32, 56):
+        monkeypatch.setenv("MINIPATH_B200_DEVICE_LEAF", str(leaf))
+        out[f"device, leaf <= {leaf}"] = _visits(ctx, mp.TriangleBvh.from_mesh(pos, tri, normals=nrm, builder=DEVICE), rays)
+    monkeypatch.delenv("MINIPATH_B200_DEVICE_LEAF")
     ctx.close()
-    print(name, out)
-    assert abs(out["device"]["hits"] - out["host"]["hits"]) <= 2e-3 * len(rays)  # same geometry up to the leaf-local quantisation
-    assert out["device"]["sectors"] <= QUALITY_FACTOR * out["host"]["sectors"]
+    for k, v in out.items():
+        print(f"QUALITY {name:7s} {k:28s} {v}")
+    d, h = out["device (default leaf size)"], out["host reference split"]
+    assert abs(d["hits"] - h["hits"]) <= 2e-3 * len(rays)  # same geometry up to the leaf-local quantisation
+    assert d["sectors"] <= QUALITY_FACTOR * h["sectors"]
