@@ -81,7 +81,9 @@ def parse_args():
     ap.add_argument("--min-batch", type=int, default=0, help="N>1 tile sharding: smallest batch of tiles a GPU claims (0 = the library's choice: about 2^20 paths)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-extra", action="store_true", help="skip the teapot-1080p (configs[1]) rider")
+    ap.add_argument("--no-extra", action="store_true", help="skip the riders (teapot-1080p = configs[1]; the default workload on the device-built tree)")
+    ap.add_argument("--builder", default="reference", choices=["reference", "device"],
+                    help="who builds the stand-in's BVH: the reference split on the host (default; the CPU arm's tree too) or mp_bvh_build_device")
     ap.add_argument("--ref-seconds", type=float, default=12.0, help="CPU arms: target seconds of oracle work per bounded step")
     ap.add_argument("--timeline", default="", help="N>1: write a per-rank timeline of one step (JSON) to this path")
     return ap.parse_args()
@@ -129,7 +131,7 @@ def workload_params(name, args):
     return scene, w, h, spp, bounces
 
 
-def load_workload(name, args):
+def load_workload(name, args, builder=None):
     """Scene (host BVH), camera and frame parameters of a workload.  Built on the host, outside every timed region
     (benches/render_teapot.rs:25-27 excludes the scene build too)."""
     import minipath_b200 as mp
@@ -145,7 +147,7 @@ def load_workload(name, args):
     else:
         from minipath_b200 import scenes
 
-        bvh, cam = scenes.atrium_scene(materials=scene.endswith("+materials"))
+        bvh, cam = scenes.atrium_scene(builder=2 if (builder or args.builder) == "device" else 0, materials=scene.endswith("+materials"))
     return bvh, cam, w, h, spp, bounces
 
 
@@ -318,11 +320,11 @@ class Timer:
         return [a.elapsed_time(b) for a, b in evs]
 
 
-def measure_single(args, name, torch, local, full=True):
+def measure_single(args, name, torch, local, full=True, builder=None):
     """N = 1: device-resident `value` through a Context, `e2e` through minipath_b200.render()."""
     import minipath_b200 as mp
 
-    bvh, cam, w, h, spp, bounces = load_workload(name, args)
+    bvh, cam, w, h, spp, bounces = load_workload(name, args, builder)
     order = mp.ORDER_REFERENCE if args.order == "reference" else mp.ORDER_NEAR_FIRST
     sampler = cam.build_sampler((w, h))
     tiles = mp.full_screen_tiles(w, h, 64)
@@ -670,6 +672,17 @@ def main():
                                       "roofline": {k: rl2[k] for k in ("bound", "achieved", "peak", "unit", "frac", "per_ray")},
                                       "note": "BASELINE configs[1] (teapot 1920x1080, 64 spp, 5 bounces), same run, same timing rules"}}
             r2["ctx"].close()
+            if args.builder == "reference":  # the same frame on the tree mp_bvh_build_device makes: fewer visits per ray
+                r3 = measure_single(args, args.workload, torch, local, full=False, builder="device")
+                rl3 = roofline(args, r3, probes)
+                st3 = r3["bvh"].stats()
+                extra[args.workload + "@device-built-tree"] = {
+                    "value": r3["value"], "unit": "Mrays/s", "ms_per_step": r3["ms_per_step"], "pipeline": r3["mode_name"], "samples_per_s": r3["samples_per_s"],
+                    "e2e": r3.get("e2e"), "bvh": {"inner_nodes": st3["n_inner"], "packets": st3["n_packets"], "device_build_ms": getattr(r3["bvh"], "last_build_ms", None)},
+                    "roofline": {k: rl3[k] for k in ("bound", "achieved", "peak", "unit", "frac", "per_ray")},
+                    "note": "same scene, camera, spp and bounces; BVH from mp_bvh_build_device (reference node format, Morton-order splits) instead of the reference split — "
+                            "samples_per_s is the comparable figure (the rays per sample are the same, the visits per ray are not)"}
+                r3["ctx"].close()
         st = res["bvh"].stats()
         line = {
             "metric": "Mrays/s", "value": res["value"], "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -679,7 +692,7 @@ def main():
             "pipeline": {"picked": res["mode_name"], "how": "MP_MODE_AUTO (what render() runs)" if args.mode == "auto" else "forced by --mode",
                          "traversal_order": args.order, "node_layout": args.layout, "pipeline_ab_ms": res["ab"],
                          "sharding": res["sharding"], "spp_total": res.get("spp_total", res["spp"]),
-                         "bvh": {"triangles": st["n_triangles"], "inner_nodes": st["n_inner"], "packets": st["n_packets"]},
+                         "bvh": {"triangles": st["n_triangles"], "inner_nodes": st["n_inner"], "packets": st["n_packets"], "builder": args.builder},
                          "per_step_ms_rank0": res["per_step_ms"], "member_stats_rank0": res.get("member_stats")},
             "rays_per_step": res["rays_job"], "gpu_launches": int(res["launches"]), "clocks": res["clocks"],
             "roofline": rl, "cpu_baseline": cb, "e2e": res.get("e2e"), "extra": extra,

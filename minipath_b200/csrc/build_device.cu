@@ -145,9 +145,9 @@ __device__ __forceinline__ uint32_t radix_split(const unsigned long long* __rest
 }
 
 // Triangles a leaf may hold.  The format allows 56 (7 packets, mod.rs:16-17), but a visited leaf tests ALL its packets: the reference's
-// cost model (0.75 per packet against 1 per inner node, building.rs:358-383) ends up near 2 packets per leaf on real scenes, and so does
-// this default (measured in profiles/r2g_device_builder_leaf_size.txt).  MINIPATH_B200_DEVICE_LEAF overrides it (8..56, a multiple of 8).
-#define DEVICE_LEAF_DEFAULT 16u
+// cost model (0.75 per packet against 1 per inner node, building.rs:358-383) ends up near 2 packets per leaf on real scenes; one packet per leaf is
+// the measured optimum here (profiles/r2g_device_builder_leaf_size.txt: fewer sectors per ray than the reference split).  MINIPATH_B200_DEVICE_LEAF overrides it (8..56, a multiple of 8).
+#define DEVICE_LEAF_DEFAULT 8u
 
 // Children of every node of one level.  node_range[first + k] is the Morton range of the level's k-th node.
 __global__ void __launch_bounds__(128) split_kernel(const unsigned long long* __restrict__ keys, const Range* __restrict__ node_range, uint32_t first,

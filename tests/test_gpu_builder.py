@@ -150,7 +150,7 @@ def test_bad_input_is_rejected():
         mp.TriangleBvh.from_mesh(pos, tri, builder=DEVICE, device=99)
 
 
-QUALITY_FACTOR = 2.0  # sectors gathered per ray on the device-built tree, at most this multiple of the host reference-split tree's
+QUALITY_FACTOR = 1.25  # sectors gathered per ray on the device-built tree, at most this multiple of the host reference-split tree's
 
 
 def _visits(ctx, bvh, rays):
