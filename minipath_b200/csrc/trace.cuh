@@ -198,7 +198,7 @@ struct StackSink {
 // MPD_INNER_SPLIT (default): the slab tests of the eight children are ONE straight-line block that ends in a hit mask, and the
 // hit children are handed to the sink afterwards, lanes ascending.  The first version tested and pushed child by child: a NULL
 // test, a branch around the test and a branch around the push per child — the compiler then re-materialised the dequantisation
-// constants behind every branch (6 of the 58 instructions a child cost, profiles/r2_sass_inner_before.txt) and could not
+// constants behind every branch (6 of the 58 instructions a child cost, profiles/r2_sass_pool_inner_before_after.txt) and could not
 // overlap the dependent chains of neighbouring children.  Same operations on the same operands, so the same bits.
 // MPD_QSEL: on the NaN-free path the near / far plane of every axis is known per RAY (sign of inv; needs min <= max per child,
 // Scene::minmax_ok), so the near and far rows are picked once per node with 24 selects instead of ordering lo / hi per child
