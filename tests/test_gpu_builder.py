@@ -29,7 +29,10 @@ def _mesh(name):
         p, t = scenes.soup_mesh(100_000)
         return p, t, None
     rng = np.random.default_rng(5)
-    if name == "one-leaf":  # <= 56 triangles: the root is a leaf link (building.rs:109-113)
+    if name == "one-leaf":  # no more triangles than the builder's leaf size: the root is a leaf link (building.rs:109-113)
+        p = rng.uniform(-1, 1, (3 * 7, 3)).astype(np.float32)
+        return p, np.arange(21, dtype=np.uint32).reshape(-1, 3), None
+    if name == "forty":
         p = rng.uniform(-1, 1, (3 * 40, 3)).astype(np.float32)
         return p, np.arange(120, dtype=np.uint32).reshape(-1, 3), None
     if name == "57":
@@ -69,18 +72,18 @@ def _rays(oracle, bvh, n_cam, n_inc, seed):
     return np.concatenate([cam, oracle.rays_from(o, d)])
 
 
-@pytest.mark.parametrize("name", ["teapot", "cube", "atrium", "soup", "one-leaf", "57", "stacked"])
+@pytest.mark.parametrize("name", ["teapot", "cube", "atrium", "soup", "one-leaf", "forty", "57", "stacked"])
 def test_device_tree_keeps_the_format_invariants(name):
     pos, tri, _, bvh = _built(name)
     check_builder_invariants(pos, tri, bvh)
     st = bvh.stats()
     assert st["n_triangles"] == len(tri) and st["max_stack"] <= 128
     if name == "one-leaf":
-        assert bvh.raw.n_inner == 0 and (bvh.raw.root & 7) == 5
+        assert bvh.raw.n_inner == 0 and (bvh.raw.root & 7) == 1
     print(name, st, "device build ms", bvh.last_build_ms)
 
 
-@pytest.mark.parametrize("name", ["teapot", "cube", "atrium", "soup", "57", "stacked"])
+@pytest.mark.parametrize("name", ["teapot", "cube", "atrium", "soup", "forty", "57", "stacked"])
 def test_oracle_and_cuda_traverse_the_device_tree_bit_equal(gpu_ctx, oracle, name):
     _, _, _, bvh = _built(name)
     rays = _rays(oracle, bvh, 128 * 128, 12000, seed=11)
