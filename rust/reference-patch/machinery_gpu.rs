@@ -3,7 +3,7 @@
 //! `finished` after its pixels are in the image; `abort()` lets in-flight tiles finish), work done by libminipath_b200.
 //! `RenderSettings` gains `max_bounces: u32` (0 = the reference shader, worker.rs:57-64) and `seed: Option<u64>`
 //! (None = OS-random like SmallRng::from_os_rng, worker.rs:25).  NOT compiled in the minipath_b200 repository.
-use std::{ffi::c_void, marker::PhantomData, sync::{Arc, Mutex}, time::Duration};
+use std::{ffi::c_void, sync::{Arc, Mutex}, time::Duration};
 
 use image::RgbaImage;
 use minipath_b200_sys as sys;
@@ -90,8 +90,11 @@ impl RenderProgress {
     pub fn abort(&self) {
         unsafe { sys::mp_progress_abort(self.handle) };
     }
+    /// Joins the worker threads.  The reference's wait() cannot fail; a device error during the render is reported here instead of being dropped.
     pub fn wait(&self) {
-        unsafe { sys::mp_progress_wait(self.handle) };
+        if let Err(e) = ok(unsafe { sys::mp_progress_wait(self.handle) }) {
+            eprintln!("render failed: {e}");
+        }
     }
     /// The image behind its mutex (machinery.rs:175-177), refreshed from the library's pinned copy under the library's image lock.
     pub fn image(&self) -> &Mutex<RgbaImage> {
@@ -114,5 +117,4 @@ impl Drop for RenderProgress {
     }
 }
 
-#[allow(dead_code)]
-struct NotUsedAnyMore(PhantomData<()>); // Worker (worker.rs) and StackCache stay for Object::intersect on single rays
+// Worker (worker.rs) and StackCache are not used on this path any more; they stay for Object::intersect on single rays.
