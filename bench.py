@@ -147,7 +147,8 @@ def load_workload(name, args, builder=None):
     else:
         from minipath_b200 import scenes
 
-        bvh, cam = scenes.atrium_scene(builder=2 if (builder or args.builder) == "device" else 0, materials=scene.endswith("+materials"))
+        bvh, cam = scenes.atrium_scene(builder=2 if (builder or args.builder) == "device" else 0, materials=scene.endswith("+materials"),
+                                       device=int(os.environ.get("LOCAL_RANK", 0)))
     return bvh, cam, w, h, spp, bounces
 
 

@@ -396,6 +396,12 @@ extern "C" int mp_bvh_build_device(int device, const float* positions, const flo
             if (tri_material[i] >= std::max(n_materials, 1u)) return mp::fail(MP_EINVAL, "triangle material %u outside the table of %u", tri_material[i], n_materials);
     int n_dev = 0;
     if (cudaGetDeviceCount(&n_dev) != cudaSuccess || device < 0 || device >= n_dev) return mp::fail(MP_ENODEVICE, "no CUDA device %d", device);
+    int prev_device = 0;
+    CKB(cudaGetDevice(&prev_device));
+    struct DeviceGuard {  // the caller's current device is restored on every path
+        int d;
+        ~DeviceGuard() { cudaSetDevice(d); }
+    } device_guard{prev_device};
     CKB(cudaSetDevice(device));
 
     // host side of the vertex records (building.rs:56-66): normals normalised, a zero normal marks its triangles flat

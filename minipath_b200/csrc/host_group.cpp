@@ -19,6 +19,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -115,7 +116,12 @@ namespace {
 
 // Guided self-scheduling: half of an equal share of what is left, at least min_batch, at most 64 tiles.
 uint64_t guided_batch(uint64_t remaining, uint32_t workers, uint32_t min_batch) {
-    const uint64_t b = remaining / (2ull * std::max(1u, workers));
+    static const uint64_t div_pct = [] {  // share of an equal split a claim takes, as its inverse in percent (200 = half); experiment knob
+        const char* e = getenv("MINIPATH_B200_GUIDED_DIV_PCT");
+        const long v = e ? atol(e) : 200;
+        return (uint64_t)(v >= 100 && v <= 1000 ? v : 200);
+    }();
+    const uint64_t b = remaining * 100ull / (div_pct * std::max(1u, workers));
     return std::max<uint64_t>(std::max(1u, min_batch), std::min<uint64_t>(64, b));
 }
 

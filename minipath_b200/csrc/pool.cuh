@@ -31,9 +31,9 @@ namespace mpd {
 #define POOL_COLS 13    // 4-byte state columns per slot
 #else
 #define POOL_VECS 0
-#define POOL_COLS 21    // 4-byte state columns per slot
+#define POOL_COLS 20    // 4-byte state columns per slot
 #endif
-#define POOL_STATE_BYTES ((POOL_VECS * 16 + POOL_COLS * 4) * POOL_W)  // per warp; 84 bytes per slot either way
+#define POOL_STATE_BYTES ((POOL_VECS * 16 + POOL_COLS * 4) * POOL_W)  // per warp; 80 bytes per slot
 #define POOL_WARPS 4    // warps per block
 #ifndef POOL_MIN_BLOCKS
 #define POOL_MIN_BLOCKS 5  // resident blocks per SM the register allocation aims at; measured: 6 (80 regs) and 8 (64 regs, 64-ray pools) are 3-15 % slower
@@ -74,7 +74,7 @@ enum {
 #if !POOL_VEC_RAY
        PC_OX, PC_OY, PC_OZ, PC_DX, PC_DY, PC_DZ, PC_IX, PC_IY,
 #endif
-       PC_IZ, PC_BT, PC_BU, PC_BV, PC_BTRI, PC_SP, PC_RID, PC_PIDX, PC_REM,
+       PC_IZ, PC_BT, PC_BU, PC_BV, PC_BTRI, PC_SP, PC_RID, PC_ITEM,  // PC_ITEM: the pending item as a CompressedNodeLink — index << 3 | packets left (0 = inner node)
        PC_LT, PC_LU, PC_LV, PC_LTRI };
 
 // Per-ray traversal stack.  Profiling the first pool kernel showed three quarters of its global L1 requests were stack pushes and
@@ -181,8 +181,7 @@ __device__ __forceinline__ uint32_t pool_next(const PoolWarp& pw, uint32_t slot,
             }
         }
         const uint32_t count = e.x & MP_LINK_COUNT_MASK;
-        pw.u(PC_PIDX, slot) = e.x >> MP_LINK_COUNT_BITS;
-        pw.u(PC_REM, slot) = count;
+        pw.u(PC_ITEM, slot) = e.x;
         if (count == 0) {
             kind = 1;
         } else {
@@ -315,7 +314,7 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
                 stk.unpack(pw.u(PC_SP, slot));
                 const Ray r = pool_load_ray(pw, slot, fixed);
                 bt = pw.f(PC_BT, slot);
-                const uint32_t node = pw.u(PC_PIDX, slot);
+                const uint32_t node = pw.u(PC_ITEM, slot) >> MP_LINK_COUNT_BITS;
                 if (COUNT) tc.vis.inner++;
                 const bool nanpath = ray_needs_nanpath(sc, r);
                 RaySel sel{};
@@ -376,7 +375,8 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
             if (act) {
                 slot = pw.ring[1 * POOL_RING + ((qs.head[1] + lane) & (POOL_RING - 1))];
                 const Ray r = pool_load_ray(pw, slot, fixed);
-                uint32_t pidx = pw.u(PC_PIDX, slot), rem = pw.u(PC_REM, slot);
+                const uint32_t item = pw.u(PC_ITEM, slot);
+                uint32_t pidx = item >> MP_LINK_COUNT_BITS, rem = item & MP_LINK_COUNT_MASK;
                 bt = pw.f(PC_BT, slot);  // = the leaf's max_t: best.t is not updated inside the leaf (:106-107)
                 Hit local{pw.f(PC_LT, slot), pw.f(PC_LU, slot), pw.f(PC_LV, slot), pw.u(PC_LTRI, slot)};
                 visit_packet<LAYOUT>(sc, r, pidx, bt, local);
@@ -385,7 +385,7 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
                     if (COUNT) tc.vis.packets -= rem;
                     rem = 0;
                 }
-                pw.u(PC_PIDX, slot) = pidx, pw.u(PC_REM, slot) = rem;
+                pw.u(PC_ITEM, slot) = pidx << MP_LINK_COUNT_BITS | rem;
                 if (rem == 0) {
                     done = true;
                     stk.ring = wring + slot, stk.spill = wstacks + slot;
@@ -488,7 +488,7 @@ __device__ __forceinline__ void pool_run_owned(const Scene& sc, uint32_t n, uint
                 stk.unpack(pw.u(PC_SP, slot));
                 const Ray r = pool_load_ray(pw, slot, fixed);
                 const float bt = pw.f(PC_BT, slot);
-                const uint32_t node = pw.u(PC_PIDX, slot);
+                const uint32_t node = pw.u(PC_ITEM, slot) >> MP_LINK_COUNT_BITS;
                 if (COUNT) tc.vis.inner++;
                 const bool nanpath = ray_needs_nanpath(sc, r);
                 RaySel sel{};
@@ -521,7 +521,8 @@ __device__ __forceinline__ void pool_run_owned(const Scene& sc, uint32_t n, uint
                 if (((kinds >> (2 * j)) & 3u) == 2u) k = j;
             const uint32_t slot = (uint32_t)k * 32u + lane;
             const Ray r = pool_load_ray(pw, slot, fixed);
-            uint32_t pidx = pw.u(PC_PIDX, slot), rem = pw.u(PC_REM, slot);
+            const uint32_t item = pw.u(PC_ITEM, slot);
+            uint32_t pidx = item >> MP_LINK_COUNT_BITS, rem = item & MP_LINK_COUNT_MASK;
             float bt = pw.f(PC_BT, slot);  // = the leaf's max_t: best.t is not updated inside the leaf (:106-107)
             Hit local{pw.f(PC_LT, slot), pw.f(PC_LU, slot), pw.f(PC_LV, slot), pw.u(PC_LTRI, slot)};
             visit_packet<LAYOUT>(sc, r, pidx, bt, local);
@@ -530,7 +531,7 @@ __device__ __forceinline__ void pool_run_owned(const Scene& sc, uint32_t n, uint
                 if (COUNT) tc.vis.packets -= rem;
                 rem = 0;
             }
-            pw.u(PC_PIDX, slot) = pidx, pw.u(PC_REM, slot) = rem;
+            pw.u(PC_ITEM, slot) = pidx << MP_LINK_COUNT_BITS | rem;
             if (rem == 0) {
                 Stack stk{nullptr, wstacks + slot, 0, 0};
                 stk.unpack(pw.u(PC_SP, slot));

@@ -154,20 +154,20 @@ def atrium_camera(bbox_min, bbox_max):
 _ATRIUM_CACHE = {}
 
 
-def atrium_scene(builder=0, materials=False):
+def atrium_scene(builder=0, materials=False, device=0):
     """(TriangleBvh, Camera) of the Sponza stand-in; the BVH uses the reference split unless builder=1.  ``materials``: with the
     per-part material table (same geometry, same tree)."""
     from . import TriangleBvh, make_materials
 
-    key = (builder, bool(materials))
+    key = (builder, bool(materials), device if builder == 2 else 0)
     if key not in _ATRIUM_CACHE:
         if materials:
             p, n, t, uv, tm, table = atrium_mesh_materials()
             mats = make_materials(table[:, :3], checker=table[:, 3] > 0, checker_scale=np.where(table[:, 3] > 0, table[:, 3], 1.0))
-            bvh = TriangleBvh.from_mesh(p, t, normals=n, builder=builder, texcoords=uv, tri_material=tm, materials=mats)
+            bvh = TriangleBvh.from_mesh(p, t, normals=n, builder=builder, texcoords=uv, tri_material=tm, materials=mats, device=device)
         else:
             p, n, t = atrium_mesh()
-            bvh = TriangleBvh.from_mesh(p, t, normals=n, builder=builder)
+            bvh = TriangleBvh.from_mesh(p, t, normals=n, builder=builder, device=device)
         _ATRIUM_CACHE[key] = (bvh, atrium_camera(*bvh.get_bounding_box()))
     return _ATRIUM_CACHE[key]
 
