@@ -347,6 +347,20 @@ int mp_trace_rays_device(MpCtx* ctx, const MpRay* dev_rays, uint64_t n, uint32_t
 /* Object::intersect including the hit finalisation (ray_bvh_intersection.rs:66-95; triangle.rs:229-244): point, shading
  * normal, material id and interpolated texture coordinates per ray — the full HitRecord, bit for bit. */
 int mp_intersect_rays(MpCtx* ctx, const MpRay* host_rays, uint64_t n, uint32_t order, MpHitRecord* host_out);
+/* mp_trace_rays_device without any allocation inside the call.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and bits as mp_trace_rays_device with MP_TRACE_POOL (dev_rays / dev_out are the caller's device buffers;
+ * asynchronous on the context's stream), but the pool kernel's scratch (per-ray traversal stacks, claim counter) lives in ONE
+ * static __device__ array of MP_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit; the persistent grid is
+ * sized to what fits.  Limits, rejected with MP_EINVAL and a message: n <= MP_NOALLOC_MAX_RAYS, and a BVH whose traversal stack
+ * needs at most MP_NOALLOC_MAX_STACK entries per ray (MpBvhStats.max_stack; the stand-in needs 108).  The scene must have been
+ * uploaded before (mp_scene_upload allocates; this call never does: no cudaMalloc / cudaFree / allocating library routine).
+ * All calls on one device share the array: the call clears what must start at zero itself, and calls that OVERLAP on the GPU
+ * (two streams, two contexts of one device) race on it — serialise them. */
+#define MP_NOALLOC_SCRATCH_BYTES 67108864u /* 64 MiB */
+#define MP_NOALLOC_MAX_STACK 128u
+#define MP_NOALLOC_MAX_RAYS 0x40000000u
+int mp_trace_rays_device_noalloc(MpCtx* ctx, const MpRay* dev_rays, uint64_t n, uint32_t order, MpHit* dev_out);
 /* CameraSampler::sample_ray (camera.rs:176-191) for every (pixel, sample) of the tiles, in
  * tile → row-major pixel → sample order; writes n_pixels*sample_count rays to the host. */
 int mp_generate_rays(MpCtx* ctx, const MpTile* tiles, uint32_t n_tiles, const MpRenderParams* params,

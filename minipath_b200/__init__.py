@@ -627,6 +627,10 @@ class Context:
         """Object::intersect on rays already resident in HBM (device pointers, e.g. torch tensors); asynchronous."""
         check(lib.mp_trace_rays_device(self._h, dev_rays, n, order, dev_hits))
 
+    def trace_rays_device_noalloc(self, dev_rays, n, dev_hits, order=ORDER_REFERENCE):
+        """mp_trace_rays_device_noalloc: the pool traversal on a static device scratch — no allocation in the call (include/minipath_b200.h)."""
+        check(lib.mp_trace_rays_device_noalloc(self._h, dev_rays, n, order, dev_hits))
+
     def generate_rays(self, tiles, params):
         arr, ptr, n = _tiles_arg(tiles)
         count = C.c_uint64()

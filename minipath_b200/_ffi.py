@@ -81,6 +81,7 @@ PROTOTYPES = {
     "mp_film_read_f32": (_i, [_vp, _vp]),
     "mp_trace_rays": (_i, [_vp, _vp, _u64, _u32, _vp]),
     "mp_trace_rays_device": (_i, [_vp, _vp, _u64, _u32, _vp]),
+    "mp_trace_rays_device_noalloc": (_i, [_vp, _vp, _u64, _u32, _vp]),
     "mp_intersect_rays": (_i, [_vp, _vp, _u64, _u32, _vp]),
     "mp_generate_rays": (_i, [_vp, _P(MpTile), _u32, _P(MpRenderParams), _vp, _u64, _P(_u64)]),
     "mp_dev_alloc": (_i, [_vp, C.c_size_t, _P(_vp)]),

@@ -477,3 +477,72 @@ int mp_film_device_ptr(MpCtx* ctx, void** out) {
 
 #include "context_render.inc"
 #include "context_probes.inc"
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// mp_trace_rays_device_noalloc — Object::intersect on device-resident rays WITHOUT any allocation in the call.
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// The pool traversal (pool.cuh) needs scratch: the per-ray stacks of every resident pool ([entry][slot] columns of 8-byte
+// entries) and the launch's claim counter.  mp_trace_rays_device takes both from cudaMalloc'ed buffers sized for the device and
+// the scene; this variant takes them from ONE file-scope array of MP_NOALLOC_SCRATCH_BYTES that every GPU loading the library
+// holds until exit, and sizes its persistent grid to what fits (a block needs POOL_WARPS * POOL_W * stack_cap * 8 bytes).
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: its device address is fetched with cudaGetSymbolAddress,
+// once per device with that device current, and THAT pointer is what the kernel gets.
+// Every call shares the array: the claim counter is cleared on the stream before each launch (stack entries are always written
+// before they are read, so they need no clearing), and two calls that overlap on the GPU (different streams or contexts of one
+// device) race on it — callers serialise them.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MP_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+unsigned char* g_noalloc_ptr[kNoallocMaxDevices] = {};  // device address of g_noalloc_scratch per device, nullptr = not asked yet
+
+// Device address of the static scratch on `device` (which must be current).
+int noalloc_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= kNoallocMaxDevices) return fail(MP_EINVAL, "device %d outside the static scratch table", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail(MP_ECUDA, "cudaGetSymbolAddress(static scratch) on device %d: %s", device, cudaGetErrorString(e));
+        g_noalloc_ptr[device] = (unsigned char*)p;
+    }
+    *out = g_noalloc_ptr[device];
+    return MP_OK;
+}
+}  // namespace
+
+extern "C" int mp_trace_rays_device_noalloc(MpCtx* ctx, const MpRay* dev_rays, uint64_t n, uint32_t order, MpHit* dev_out) {
+    if (int rc = use_device(ctx)) return rc;
+    if (!ctx->has_scene) return fail(MP_ESTATE, "no scene uploaded");
+    if (order > MP_ORDER_NEAR_FIRST) return fail(MP_EINVAL, "bad order");
+    if (n == 0) return MP_OK;
+    if (!dev_rays || !dev_out) return fail(MP_EINVAL, "null buffer");
+    if (n > MP_NOALLOC_MAX_RAYS) return fail(MP_EINVAL, "%llu rays in one call; the no-allocation entry point takes at most %llu", (unsigned long long)n, (unsigned long long)MP_NOALLOC_MAX_RAYS);
+    const uint32_t cap = std::max<uint32_t>(8, (ctx->max_stack + 3u) & ~3u);
+    if (cap > MP_NOALLOC_MAX_STACK)
+        return fail(MP_EINVAL, "this BVH needs a %u-entry traversal stack per ray; the static scratch serves at most %u (use mp_trace_rays_device)", cap, (unsigned)MP_NOALLOC_MAX_STACK);
+    unsigned char* base = nullptr;
+    if (int rc = noalloc_scratch(ctx->device, &base)) return rc;
+    uint32_t* claim = reinterpret_cast<uint32_t*>(base);            // first 256 bytes: the claim counter
+    uint2* stacks = reinterpret_cast<uint2*>(base + 256);
+    const size_t per_block = (size_t)POOL_WARPS * POOL_W * cap * sizeof(uint2);
+    const unsigned long long fit = (MP_NOALLOC_SCRATCH_BYTES - 256) / per_block;  // >= 1 by the two limits above
+    const bool dec = effective_layout(ctx, false) == MP_LAYOUT_DECODED;
+    const unsigned long long resident = (unsigned long long)ctx->sm_count * (dec ? POOL_MIN_BLOCKS_DECODED : POOL_MIN_BLOCKS);
+    const unsigned long long need = (n + POOL_WARPS * 32 - 1) / (POOL_WARPS * 32);
+    const unsigned blocks = (unsigned)std::max<unsigned long long>(1, std::min(std::min(need, resident), fit));
+    const size_t smem = (size_t)POOL_WARPS * POOL_SMEM_PER_WARP;
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    CK(cudaMemsetAsync(claim, 0, 256, ctx->stream));
+    const float* r = (const float*)dev_rays;
+    uint4* h = (uint4*)dev_out;
+    MP_DISPATCH(ctx, false, order, mpd::trace_rays_pool_kernel<L, O, C><<<blocks, 128, smem, ctx->stream>>>(ctx->scene, r, (uint32_t)n, h, ctx->d_counters, claim, stacks, cap));
+    ctx->launches++;
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->timed = true;
+    CK(cudaGetLastError());
+    return MP_OK;
+}

@@ -95,6 +95,9 @@ pub struct MpMaterial {
     pub _pad: [f32; 3],
 }
 pub const MP_MAT_CHECKER: u32 = 1;
+pub const MP_NOALLOC_SCRATCH_BYTES: u32 = 67108864;
+pub const MP_NOALLOC_MAX_STACK: u32 = 128;
+pub const MP_NOALLOC_MAX_RAYS: u64 = 0x40000000;
 pub const MP_TRI_MATERIAL_MASK: u32 = 0x7fff_ffff;
 pub const MP_DEFAULT_ALBEDO: f32 = 0.7;
 pub const MP_DEFAULT_CHECKER_SCALE: f32 = 4.0;
@@ -338,6 +341,7 @@ extern "C" {
     // Object::intersect on caller rays (scene/mod.rs:7-10) and CameraSampler::sample_ray dumps (camera.rs:176-191)
     pub fn mp_trace_rays(ctx: *mut MpCtx, host_rays: *const MpRay, n: u64, order: u32, host_out: *mut MpHit) -> c_int;
     pub fn mp_trace_rays_device(ctx: *mut MpCtx, dev_rays: *const MpRay, n: u64, order: u32, dev_out: *mut MpHit) -> c_int;
+    pub fn mp_trace_rays_device_noalloc(ctx: *mut MpCtx, dev_rays: *const MpRay, n: u64, order: u32, dev_out: *mut MpHit) -> c_int;
     pub fn mp_intersect_rays(ctx: *mut MpCtx, host_rays: *const MpRay, n: u64, order: u32, host_out: *mut MpHitRecord) -> c_int;
     pub fn mp_generate_rays(ctx: *mut MpCtx, tiles: *const MpTile, n_tiles: u32, params: *const MpRenderParams, host_out: *mut MpRay, cap: u64, out_n: *mut u64) -> c_int;
 
