@@ -19,7 +19,7 @@
 namespace mpd {
 
 #ifndef POOL_W
-#define POOL_W 96       // ray slots per warp
+#define POOL_W 80       // ray slots per warp (round 2: 96 -> 80 together with 7 blocks per SM, profiles/r2o_variants_pool_occupancy.txt)
 #endif
 #define POOL_RING 128   // ring capacity (power of two >= POOL_W)
 #ifndef POOL_VEC_RAY
@@ -36,7 +36,10 @@ namespace mpd {
 #define POOL_STATE_BYTES ((POOL_VECS * 16 + POOL_COLS * 4) * POOL_W)  // per warp; 80 bytes per slot
 #define POOL_WARPS 4    // warps per block
 #ifndef POOL_MIN_BLOCKS
-#define POOL_MIN_BLOCKS 5  // resident blocks per SM the register allocation aims at; measured: 6 (80 regs) and 8 (64 regs, 64-ray pools) are 3-15 % slower
+#define POOL_MIN_BLOCKS 7  // resident blocks per SM the register allocation aims at.  The kernel waits on L2 round trips (long_scoreboard is the largest stall,
+                           // 5 warps per scheduler issue 65 % of the cycles): since the inner-node code lost its branches, 72 registers cost 36 bytes of spills and
+                           // 28 warps per SM beat 20 (round 1 measured 6 / 8 blocks slower: 80 / 64 registers spilled much more then).  7 blocks x 80-ray pools x 80 B
+                           // of state fit the 228 KB shared-memory configuration.
 #endif
 #ifndef POOL_MIN_BLOCKS_DECODED
 #define POOL_MIN_BLOCKS_DECODED 4  // the DECODED instantiations serve BVHs of at most 1 MB (AUTO layout), which live in L1: there 4 blocks (102 registers)
@@ -407,6 +410,10 @@ __device__ __forceinline__ void pool_run(const Scene& sc, uint32_t n, uint32_t* 
     }
 }
 
+#ifndef POOL_LANE_OWNED
+#define POOL_LANE_OWNED 0
+#endif
+#define POOL_LANE_OWNED_CHECK POOL_LANE_OWNED
 #ifndef POOL_OWNED_REFILL
 #define POOL_OWNED_REFILL 32u  // free slots in the warp that trigger a refill (one atomicAdd on the launch's claim counter)
 #endif
@@ -421,7 +428,7 @@ __device__ __forceinline__ void pool_run_owned(const Scene& sc, uint32_t n, uint
                                                unsigned char* smem, Fetch fetch, Emit emit, ThreadCounts& tc, const Ray* fixed = nullptr) {
     constexpr uint32_t FULL = 0xffffffffu;
     constexpr int K = POOL_W / 32;  // slots per lane
-    static_assert(POOL_W % 32 == 0 && K <= 8, "lane-owned pools hold a whole number of slots per lane");
+    static_assert(!POOL_LANE_OWNED_CHECK || (POOL_W % 32 == 0 && K <= 8), "lane-owned pools hold a whole number of slots per lane");
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     PoolWarp pw;
     pw.vec = reinterpret_cast<float4*>(smem + (size_t)warp * POOL_SMEM_PER_WARP);

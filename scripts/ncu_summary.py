@@ -21,6 +21,10 @@ def main(path):
     for i,h in enumerate(hdr):
         if h not in WANT and (h.startswith('l1tex__data_pipe_lsu_wavefronts') or h.startswith('l1tex__t_sectors_pipe_lsu_mem_global_op') or h.startswith('l1tex__t_requests_pipe_lsu_mem_global_op')):
             print(f'{h} [{units[i]}]', [r[i] for r in rows[2:]])
+    for i,h in enumerate(hdr):  # warps stalled per issue cycle, by reason (sums to the warp latency per instruction issued)
+        if 'issue_stalled' in h and h.endswith('_per_issue_active.ratio') and 'not_issued' not in h:
+            vals=[float(r[i] or 0) for r in rows[2:]]
+            if max(vals) > 0.15: print('stall/issue:', h.replace('smsp__average_warps_issue_stalled_','').replace('smsp__average_warp_latency_issue_stalled_','').replace('_per_issue_active.ratio',''), [round(v,2) for v in vals])
     for i,h in enumerate(hdr):
         if 'warp_issue_stalled' in h and h.endswith('_per_warp_active.pct'):
             vals=[float(r[i]) for r in rows[2:]]
