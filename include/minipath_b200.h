@@ -426,7 +426,8 @@ int mp_tileq_close(MpTileQueue* q, int unlink);
 
 /* ---- multi-GPU groups: render()'s scheduler over the GPUs of one box (machinery.rs:51-116,205-209) ----
  * Workers = GPUs.  MP_SHARD_TILES: the devices pull batches of consecutive tiles of the tile list from ONE shared counter
- * (remaining / (2 * devices) tiles at a time, at least min_batch — 0 = as many tiles as carry 2^20 paths —: coarse while work is plentiful, fine at the tail) — total work
+ * (a device's first claim is 3/4 of an equal share in one piece, then remaining / (2 * devices) tiles at a time, at least min_batch — 0 = as many tiles
+ * as carry 2^20 paths —: coarse while work is plentiful, fine at the tail) — total work
  * fixed, "strong" scaling (BASELINE configs[2]).  MP_SHARD_SPP: every device renders all tiles with its own contiguous slice of
  * the sample indices (BASELINE configs[3]).  Either way each device accumulates into its own zero-initialised full-resolution
  * film and ONE ncclReduce(sum, f32 x 4 per pixel) over NVLink combines them on rank 0, which resolves.  No traffic between GPUs

@@ -114,7 +114,7 @@ struct MpGroup {
 
 namespace {
 
-// Guided self-scheduling: half of an equal share of what is left, at least min_batch, at most 64 tiles.
+// Guided self-scheduling after a worker's first claim: half of an equal share of what is left, at least min_batch, at most 64 tiles.
 uint64_t guided_batch(uint64_t remaining, uint32_t workers, uint32_t min_batch) {
     static const uint64_t div_pct = [] {  // share of an equal split a claim takes, as its inverse in percent (200 = half); experiment knob
         const char* e = getenv("MINIPATH_B200_GUIDED_DIV_PCT");
@@ -125,7 +125,20 @@ uint64_t guided_batch(uint64_t remaining, uint32_t workers, uint32_t min_batch) 
     return std::max<uint64_t>(std::max(1u, min_batch), std::min<uint64_t>(64, b));
 }
 
-int claim(MpGroup* g, uint64_t total, uint32_t min_batch, uint64_t* first, uint64_t* n) {
+// A worker's FIRST claim of a frame: a fixed share of an equal split in one piece.  Small batches run narrower wavefront passes (measured on
+// 8 GPUs, profiles/r2q_timeline_*: 3.47 ms per tile in 64-tile batches, 3.7 ms in the 8..31-tile batches of the guided sequence), while the tail
+// only has to absorb the +-5 % by which equal tile counts differ in cost — so most of a worker's tiles come in one wide batch and the
+// guided sequence shares out the rest.
+uint64_t first_share(uint64_t total, uint32_t workers) {
+    static const uint64_t pct = [] {
+        const char* e = getenv("MINIPATH_B200_FIRST_SHARE_PCT");
+        const long v = e ? atol(e) : 75;
+        return (uint64_t)(v >= 0 && v <= 100 ? v : 75);
+    }();
+    return total * pct / (100ull * std::max(1u, workers));
+}
+
+int claim(MpGroup* g, uint64_t total, uint32_t min_batch, bool first_claim, uint64_t* first, uint64_t* n) {
     uint64_t cur = 0;
     if (g->queue) {
         if (int rc = mp_tileq_peek(g->queue, &cur)) return rc;
@@ -136,7 +149,8 @@ int claim(MpGroup* g, uint64_t total, uint32_t min_batch, uint64_t* first, uint6
         *first = total, *n = 0;
         return MP_OK;
     }
-    const uint64_t want = guided_batch(total - cur, (uint32_t)g->world, min_batch);
+    uint64_t want = guided_batch(total - cur, (uint32_t)g->world, min_batch);
+    if (first_claim) want = std::max(want, std::min(first_share(total, (uint32_t)g->world), total - cur));
     uint64_t f = 0;
     if (g->queue) {
         if (int rc = mp_tileq_next(g->queue, want, &f)) return rc;
@@ -171,7 +185,7 @@ int member_render(MpGroup* g, Member& m, const MpTile* tiles, uint32_t n_tiles, 
         for (int k = 0;; k ^= 1) {
             if (m.batches >= 2) CU_CK(cudaEventSynchronize(m.done[k]));  // the batch before the previous one has left the device
             uint64_t first = 0, n = 0;
-            if (int rc = claim(g, n_tiles, min_batch, &first, &n)) return rc;
+            if (int rc = claim(g, n_tiles, min_batch, m.batches == 0, &first, &n)) return rc;
             if (n == 0) break;
             if (int rc = mp_render_tile_range(m.ctx, (uint32_t)first, (uint32_t)n, p)) return rc;  // worker.render_tile (machinery.rs:77)
             CU_CK(cudaEventRecord(m.done[k], (cudaStream_t)stream));
