@@ -264,7 +264,9 @@ int mp_render(const MpFlatBvh* scene, const MpCamera* camera, const MpRenderSett
         MpBvhStats st;
         const bool have = mp_bvh_stats(scene, &st) == MP_OK;
         const bool deep = have && st.max_stack > 128;
-        if (deep) p->trace_variant = MP_TRACE_OCTET;
+        // deep trees: the pool kernel keeps its stacks in global scratch (any depth) and is the fast one; OCTET (3-4x the instructions) only serves
+        // callers that ask for it.  The megakernel cannot run them (128-entry local stack), so a forced MP_MODE_MEGAKERNEL fails in launch_render.
+        if (deep) p->trace_variant = MP_TRACE_POOL;
         if (p->settings.mode == MP_MODE_AUTO) {
             // measured: primary rays only → megakernel (2.6 vs 3.0 ms on the reference's bench workload); a scene that is one
             // leaf → megakernel (cube 13.1 vs 17.2 ms); otherwise the wavefront pipeline with pooled incoherent rays (teapot 32.0 vs 47.1 ms,
