@@ -116,7 +116,7 @@ __device__ __forceinline__ bool tri_lane(const uint4 (&q)[9], int lane, const F3
 // width (profiles/r1b_ubench_l1_patterns.txt: 10 x LDG.128 = 9.3 clk per node and SM, 5 x LDG.256 = 4.9), so the quantised
 // records are read 32 bytes at a time.
 // MPD_LD_NODE / MPD_LD_PACKET pick the L1 eviction policy of the record loads (0 default, 1 evict_last, 2 no_allocate,
-// 3 evict_first): an A/B switch for scripts/build_variant.sh, measured in profiles/r2c_variants_cache_policy.txt.
+// 3 evict_first): an A/B switch for scripts/build_variant.sh, measured in profiles/r2c_variants_pool_levers.txt.
 #ifndef MPD_LD_NODE
 #define MPD_LD_NODE 0
 #endif
