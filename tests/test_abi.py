@@ -66,3 +66,31 @@ def test_render_rejects_bad_mode_and_kernel():
         assert e.value.code == mp._ffi.MP_EINVAL, kw
     assert mp.RenderSettings(64, 1, (64, 64))._raw().mode == mp.MODE_AUTO
     assert mp.RenderSettings(64, 1, (64, 64)).params().mode == mp.MODE_MEGAKERNEL
+
+
+def test_device_entry_points_fail_loudly_without_a_gpu():
+    """No CPU fallback anywhere: on a box without a CUDA device the device entry points return an error code and a message."""
+    import ctypes as C
+
+    import numpy as np
+
+    import minipath_b200 as mp
+    from minipath_b200 import _ffi
+
+    if mp.device_count() > 0:
+        pytest.skip("this box has a GPU")
+    lib = _ffi.lib
+    out = C.c_void_p()
+    assert lib.mp_ctx_create(0, C.byref(out)) == _ffi.MP_ENODEVICE and b"no CUDA device" in lib.mp_last_error()
+    assert lib.mp_trace_rays_device_noalloc(None, None, 1, 0, None) == _ffi.MP_EINVAL
+    pos = np.zeros((3, 3), np.float32)
+    tri = np.array([[0, 1, 2]], np.uint32)
+    bvh = C.POINTER(_ffi.MpFlatBvh)()
+    fp, up = C.POINTER(C.c_float), C.POINTER(C.c_uint32)
+    rc = lib.mp_bvh_build_device(0, pos.ctypes.data_as(fp), None, None, 3, tri.ctypes.data_as(up), None, 1, None, 0, C.byref(bvh), None)
+    assert rc == _ffi.MP_ENODEVICE, lib.mp_last_error()
+    dev = (C.c_int * 1)(0)
+    grp = C.c_void_p()
+    assert lib.mp_group_create(dev, 1, C.byref(grp)) != _ffi.MP_OK
+    with pytest.raises(mp.MpError):
+        mp.render(mp.Scene(mp.TriangleBvh.with_obj(os.path.join(ROOT, "data", "teapot.obj"))), mp.Camera.default(), mp.RenderSettings(64, 1, (64, 64))).wait()
