@@ -632,6 +632,13 @@ def run_probes(ctx, bvh):
                       + ("measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)")}
 
 
+def rider_probes(probes, ctx, bvh):
+    """A rider's own L1-gather roof: the sector rate depends on whether the record table fits L1 (profiles/r2c_l1_gather_sweep.txt), so the main
+    workload's probe must not be reused for a scene of another size; the other roofs do not depend on the scene."""
+    raw = bvh.raw
+    return dict(probes, l1_gather_gsectors=ctx.probe_l1_gather(max(1024, int(raw.n_inner + raw.n_packets)), 5))
+
+
 def main():
     args = parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -667,7 +674,7 @@ def main():
         extra = None
         if world == 1 and not args.no_extra and args.workload == DEFAULT_WORKLOAD:
             r2 = measure_single(args, "teapot-1080p", torch, local, full=False)
-            rl2 = roofline(args, r2, probes)
+            rl2 = roofline(args, r2, rider_probes(probes, r2["ctx"], r2["bvh"]))
             extra = {"teapot-1080p": {"config": workload_config("teapot-1080p", args), "value": r2["value"], "unit": "Mrays/s", "ms_per_step": r2["ms_per_step"],
                                       "pipeline": r2["mode_name"], "samples_per_s": r2["samples_per_s"], "e2e": r2.get("e2e"),
                                       "roofline": {k: rl2[k] for k in ("bound", "achieved", "peak", "unit", "frac", "per_ray")},
@@ -675,7 +682,7 @@ def main():
             r2["ctx"].close()
             if args.builder == "reference":  # the same frame on the tree mp_bvh_build_device makes: fewer visits per ray
                 r3 = measure_single(args, args.workload, torch, local, full=False, builder="device")
-                rl3 = roofline(args, r3, probes)
+                rl3 = roofline(args, r3, rider_probes(probes, r3["ctx"], r3["bvh"]))
                 st3 = r3["bvh"].stats()
                 extra[args.workload + "@device-built-tree"] = {
                     "value": r3["value"], "unit": "Mrays/s", "ms_per_step": r3["ms_per_step"], "pipeline": r3["mode_name"], "samples_per_s": r3["samples_per_s"],
